@@ -1,0 +1,164 @@
+/*
+ * doma_b200.h — C ABI of the B200-native DOMA sweep hot path.
+ *
+ * One context = one problem (mesh + materials + this rank's ordinates) resident on ONE GPU.
+ * Every entry point replaces one private member of the reference's
+ * TransportSolver3D<T> / TransportSolver2D<T> (citations are relative to the DOMA source tree;
+ * "3D" = src/TransportSolver3D.cpp, "2D" = src/TransportSolver2D.cpp).  The reference has no FFI;
+ * its only extension point is the template parameter T (include/TransportSolver3D.h:12-16,112-113),
+ * so the boundary sits on the members that call T::solve.  INTEGRATION.md shows the
+ * explicit-specialisation seam that binds these calls under the reference's unmodified loops.
+ *
+ * Conventions
+ *  - plain pointers and sizes only; every function returns 0 on success, non-zero on error
+ *    (message via doma_b200_last_error); nothing throws across the boundary.
+ *  - all host pointers are read (or written) during the call only; the context owns device memory.
+ *  - one calling thread per context; calls are ordered on the context's CUDA stream; calls that
+ *    return a scalar or copy to the host synchronise that stream.
+ *  - all floating point is IEEE binary64, as in the reference.
+ *  - there is NO CPU fallback: create fails if no CUDA device is usable.
+ */
+#ifndef DOMA_B200_H
+#define DOMA_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* include/TransportBase.h:20-30 (Octant), :38-43 (RunMode), :45-49 (EquationType), :57-62 (StepType) */
+enum { DOMA_OCT_PPP = 0, DOMA_OCT_PPM, DOMA_OCT_PMP, DOMA_OCT_PMM, DOMA_OCT_MPP, DOMA_OCT_MPM, DOMA_OCT_MMP, DOMA_OCT_MMM };
+enum { DOMA_MODE_FIXED = 0, DOMA_MODE_EIGEN = 1, DOMA_MODE_TRANSIENT = 2 };
+enum { DOMA_SCHEME_DD = 0, DOMA_SCHEME_TWDD = 1 };
+enum { DOMA_STEP_NONE = -1, DOMA_STEP_INSERT = 0, DOMA_STEP_REMOVE = 1, DOMA_STEP_BOTH = 2 };
+/* mat_flags bits: which optional MaterialProps vectors are non-empty (include/InputParameters.h:26-52) */
+enum { DOMA_MAT_HAS_SRC = 1, DOMA_MAT_HAS_CHI_P = 2, DOMA_MAT_HAS_NU_SIGMA_F = 4 };
+
+/*
+ * Flat, caller-owned problem description; copied at create.
+ * Cell order is the reference's: index = k*ny*nx + j*nx + i, x fastest (src/BrickMesh3D.cpp:86-102).
+ * G = n_groups, D = n_delayed_max, M = n_mat.
+ */
+typedef struct doma_b200_problem
+{
+  int32_t dims;               /* 2 or 3 */
+  int32_t nx, ny, nz;         /* total cells per axis (BrickMesh3D::_tot_num_x/y/z); nz = 1 in 2D */
+  const double * dx;          /* [nx] per-cell x widths (CartesianCell3D::_l_x, src/BrickMesh3D.cpp:44-49) */
+  const double * dy;          /* [ny] */
+  const double * dz;          /* [nz] (ignored in 2D) */
+  const int32_t * mat_of_cell;/* [nx*ny*nz] dense material index of each cell (from _block_id) */
+
+  int32_t n_groups;
+  int32_t n_mat;
+  int32_t n_delayed_max;      /* D: max MaterialProps::_num_d_groups over materials (0 outside transients) */
+  const int32_t * mat_flags;  /* [M] DOMA_MAT_HAS_* */
+  const int32_t * n_delayed;  /* [M] MaterialProps::_num_d_groups */
+  const double * sigma_t;     /* [M*G]   _g_total */
+  const double * sigma_s;     /* [M*G*G] _g_g_scatter_mat, [to*G+from] after any transpose (src/InputParameters.cpp:301-318) */
+  const double * nu_sigma_f;  /* [M*G]   _g_prod   (zeros when absent) */
+  const double * chi_p;       /* [M*G]   _g_chi_p  (zeros when absent) */
+  const double * src;         /* [M*G]   _g_src    (zeros when absent) */
+  const double * inv_v;       /* [M*G]   _g_inv_v  (zeros when absent) */
+  const double * chi_d;       /* [M*G*D] _n_g_chi_d re-strided to [g*D+d] */
+  const double * beta;        /* [M*G*D] _g_n_beta  re-strided to [g*D+d] */
+  const double * lambda;      /* [M*D]   _n_lambda */
+  const int32_t * step_type;  /* [M] DOMA_STEP_* of the block's SourceStep (include/InputParameters.h:10-22) */
+  const double * step_t_insert; /* [M] */
+  const double * step_t_remove; /* [M] */
+  const double * step_src;    /* [M*G] */
+
+  /* This context's ordinates (the caller shards them across ranks), signed exactly as
+   * GCAngularQuadrature::direction returns them (src/GCAngularQuadrature.cpp:58-64). */
+  int32_t n_ord;
+  const int32_t * ord_octant; /* [n_ord] DOMA_OCT_* */
+  const double * mu;          /* [n_ord] */
+  const double * eta;         /* [n_ord] */
+  const double * xi;          /* [n_ord] */
+  const double * w;           /* [n_ord] */
+
+  int32_t scheme;             /* DOMA_SCHEME_* (XML scheme=, src/main.cpp:208,250) */
+  int32_t mode;               /* DOMA_MODE_*   (TransportSolver3D::_mode) */
+  double dt;                  /* TransportSolver3D::_dt; read only in transient mode */
+  int32_t device;             /* CUDA device ordinal */
+} doma_b200_problem;
+
+typedef struct doma_b200_ctx doma_b200_ctx;
+
+/* lifetime -------------------------------------------------------------------------------------- */
+int doma_b200_create(const doma_b200_problem * problem, doma_b200_ctx ** out);
+int doma_b200_destroy(doma_b200_ctx * ctx);
+const char * doma_b200_last_error(const doma_b200_ctx * ctx); /* ctx may be NULL: last create error */
+/* run the context on a caller-provided CUDA stream (cudaStream_t as void*); NULL = the context's own */
+int doma_b200_set_stream(doma_b200_ctx * ctx, void * cuda_stream);
+int doma_b200_synchronize(doma_b200_ctx * ctx);
+
+/* state management ------------------------------------------------------------------------------ */
+/* initializeSolve (3D:499-529): phi_tot[g] = phi_init (1.0 eigen / 0.0 otherwise), phi_prev = 0, q = 0, phi_cur = 0 */
+int doma_b200_reset_state(doma_b200_ctx * ctx, double phi_init);
+/* initZeroIC (3D:140-156): phi_tot, phi_prev, phi_last, dnp_cur, dnp_last = 0 (q and phi_cur untouched) */
+int doma_b200_init_zero_ic(doma_b200_ctx * ctx);
+/* updateStepFluxes (3D:212-234): phi_last = phi_tot; phi_tot = 0; q = 0; phi_cur = 0 */
+int doma_b200_update_step_fluxes(doma_b200_ctx * ctx);
+/* stepDNPs (3D:236-260): analytic precursor step with exp(-lambda*dt) */
+int doma_b200_step_dnps(doma_b200_ctx * ctx);
+
+/* source build ---------------------------------------------------------------------------------- */
+/* updateMultigroupSource(g,t) (3D:339-402, 2D same lines with 0.5/pi) */
+int doma_b200_update_mg_source(doma_b200_ctx * ctx, int32_t g, double t);
+/* updateMultigroupSourceEigen(g) (3D:404-430); q is accumulated ("+="); k = TransportSolver3D::_k */
+int doma_b200_update_mg_source_eigen(doma_b200_ctx * ctx, int32_t g, double k);
+/* updateScatteringSource(g) (3D:531-545) */
+int doma_b200_update_scatter_source(doma_b200_ctx * ctx, int32_t g);
+
+/* sweep ----------------------------------------------------------------------------------------- */
+/* sweep(g) (3D:565-622, 2D:565-602): phi_cur[c] += sum over this context's ordinates of w*psi_c.
+ * With ordinates sharded over ranks the caller sums phi_cur across ranks afterwards
+ * (doma_b200_device_ptr(DOMA_PTR_PHI_CUR) + an all-reduce on the same stream). */
+int doma_b200_sweep(doma_b200_ctx * ctx, int32_t g);
+
+/* reductions (each synchronises and returns scalars) ------------------------------------------- */
+/* computeScatteringResidual(g) (3D:547-563) */
+int doma_b200_scatter_residual(doma_b200_ctx * ctx, int32_t g, double * out);
+/* computeMGFluxResidual() (3D:318-337) */
+int doma_b200_mg_residual(doma_b200_ctx * ctx, double * out);
+/* updateEigenvalue() (3D:432-456): k_prev_out = *k_inout; *k_inout = num/den */
+int doma_b200_update_k(doma_b200_ctx * ctx, double * k_inout, double * k_prev_out);
+
+/* host <-> device state ------------------------------------------------------------------------- */
+enum
+{
+  DOMA_ARR_PHI_TOT = 0,  /* CartesianCell3D::_total_scalar_flux[g]      index = group */
+  DOMA_ARR_PHI_PREV = 1, /* _prev_mg_scalar_flux[g]                     index = group */
+  DOMA_ARR_PHI_LAST = 2, /* _last_t_scalar_flux[g]                      index = group */
+  DOMA_ARR_DNP_CUR = 3,  /* _current_t_dnps[d]                          index = delayed group */
+  DOMA_ARR_DNP_LAST = 4, /* _last_t_dnps[d]                             index = delayed group */
+  DOMA_ARR_Q = 5,        /* _current_iteration_source                   index ignored */
+  DOMA_ARR_PHI_CUR = 6   /* _current_scalar_flux                        index ignored */
+};
+/* copy one per-cell array (N doubles, reference cell order) device -> host / host -> device */
+int doma_b200_get_array(doma_b200_ctx * ctx, int32_t which, int32_t index, double * host_out);
+int doma_b200_set_array(doma_b200_ctx * ctx, int32_t which, int32_t index, const double * host_in);
+/* raw device pointer of a per-cell array (for stream-ordered collectives by the host layer) */
+int doma_b200_device_ptr(doma_b200_ctx * ctx, int32_t which, int32_t index, void ** out);
+
+/* introspection --------------------------------------------------------------------------------- */
+enum
+{
+  DOMA_INFO_KERNEL_LAUNCHES = 0, /* kernels launched by this context so far */
+  DOMA_INFO_SWEEP_VARIANT = 1,   /* 0 = hyperplane-per-launch, 1 = persistent KBA tiles */
+  DOMA_INFO_N_CELLS = 2,
+  DOMA_INFO_N_ORD = 3,
+  DOMA_INFO_FACE_BYTES = 4,
+  DOMA_INFO_DEVICE_BYTES = 5
+};
+int doma_b200_get_info(doma_b200_ctx * ctx, int32_t what, int64_t * out);
+/* select the sweep implementation (see DOMA_INFO_SWEEP_VARIANT); default 1 */
+int doma_b200_set_sweep_variant(doma_b200_ctx * ctx, int32_t variant);
+/* device time in ms of the most recent doma_b200_sweep (CUDA events on the context's stream; synchronises) */
+int doma_b200_last_sweep_ms(doma_b200_ctx * ctx, float * out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DOMA_B200_H */
