@@ -1,0 +1,647 @@
+// api.cu — the C ABI of include/doma_b200.h: context lifetime, host<->device state, reductions'
+// host side, the NCCL phi all-reduce.  No torch types, plain pointers and sizes.
+#include "ctx.h"
+
+#include <dlfcn.h>
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <vector>
+
+namespace
+{
+char g_create_err[DOMA_MAX_ERR] = "";
+
+template <typename T>
+int
+upload(doma_b200_ctx * c, T ** dst, const T * src, size_t n, T fill = T())
+{
+  *dst = nullptr;
+  const size_t cnt = n ? n : 1;
+  DOMA_CUDA(c, cudaMalloc((void **)dst, sizeof(T) * cnt));
+  c->device_bytes += sizeof(T) * cnt;
+  std::vector<T> tmp(cnt, fill);
+  if (src && n)
+    memcpy(tmp.data(), src, sizeof(T) * n);
+  DOMA_CUDA(c, cudaMemcpy(*dst, tmp.data(), sizeof(T) * cnt, cudaMemcpyHostToDevice));
+  return 0;
+}
+
+int
+alloc_zero(doma_b200_ctx * c, double ** dst, size_t n)
+{
+  *dst = nullptr;
+  const size_t cnt = n ? n : 1;
+  DOMA_CUDA(c, cudaMalloc((void **)dst, sizeof(double) * cnt));
+  DOMA_CUDA(c, cudaMemset(*dst, 0, sizeof(double) * cnt));
+  c->device_bytes += sizeof(double) * cnt;
+  return 0;
+}
+
+// Regroup this context's ordinates into sweep units: per octant, ceil(count/32) batches of
+// near-equal size; lanes beyond a batch are padded with a harmless direction and weight 0.
+int
+build_units(doma_b200_ctx * c, const doma_b200_problem * p)
+{
+  std::vector<int> uo;
+  std::vector<double> mu, eta, xi, w;
+  std::vector<SweepUnit> units;
+  for (int oct = 0; oct < 8; ++oct)
+  {
+    std::vector<int> idx;
+    for (int n = 0; n < p->n_ord; ++n)
+      if (p->ord_octant[n] == oct)
+        idx.push_back(n);
+    if (idx.empty())
+      continue;
+    if (c->dims == 2 && (oct & 1))
+    {
+      snprintf(c->err, DOMA_MAX_ERR, "create: 2D problems sweep only the xi>0 octants (PPP, PMP, MPP, MMP); got octant %d", oct);
+      return 9;
+    }
+    const int cnt = (int)idx.size();
+    const int nb = (cnt + DOMA_LANES - 1) / DOMA_LANES;
+    int pos = 0;
+    for (int b = 0; b < nb; ++b)
+    {
+      const int sz = cnt / nb + (b < cnt % nb ? 1 : 0);
+      units.push_back(SweepUnit{oct, sz});
+      uo.push_back(oct);
+      for (int l = 0; l < DOMA_LANES; ++l)
+      {
+        if (l < sz)
+        {
+          const int n = idx[pos + l];
+          // parallelSweepOctant takes std::abs of each component (src/TransportSolver3D.cpp:645-649)
+          mu.push_back(fabs(p->mu[n]));
+          eta.push_back(fabs(p->eta[n]));
+          xi.push_back(fabs(p->xi[n]));
+          w.push_back(p->w[n]);
+        }
+        else
+        {
+          mu.push_back(1.0);
+          eta.push_back(1.0);
+          xi.push_back(1.0);
+          w.push_back(0.0);
+        }
+      }
+      pos += sz;
+    }
+  }
+  c->n_units = (int)units.size();
+  c->h_units = (SweepUnit *)malloc(sizeof(SweepUnit) * (units.size() + 1));
+  memcpy(c->h_units, units.data(), sizeof(SweepUnit) * units.size());
+  int rc = 0;
+  if ((rc = upload(c, &c->unit_octant, uo.data(), uo.size())))
+    return rc;
+  if ((rc = upload(c, &c->u_mu, mu.data(), mu.size())))
+    return rc;
+  if ((rc = upload(c, &c->u_eta, eta.data(), eta.size())))
+    return rc;
+  if ((rc = upload(c, &c->u_xi, xi.data(), xi.size())))
+    return rc;
+  if ((rc = upload(c, &c->u_w, w.data(), w.size())))
+    return rc;
+  return 0;
+}
+
+int
+create_impl(doma_b200_ctx * c, const doma_b200_problem * p)
+{
+  int n_dev = 0;
+  DOMA_CUDA(c, cudaGetDeviceCount(&n_dev));
+  if (n_dev < 1 || p->device < 0 || p->device >= n_dev)
+  {
+    snprintf(c->err, DOMA_MAX_ERR, "create: CUDA device %d not available (%d devices); there is no CPU fallback", p->device, n_dev);
+    return 2;
+  }
+  c->device = p->device;
+  DOMA_CUDA(c, cudaSetDevice(c->device));
+  cudaDeviceProp prop;
+  DOMA_CUDA(c, cudaGetDeviceProperties(&prop, c->device));
+  c->n_sms = prop.multiProcessorCount;
+  c->dims = p->dims;
+  c->nx = p->nx, c->ny = p->ny, c->nz = p->dims == 3 ? p->nz : 1;
+  c->N = (int64_t)c->nx * c->ny * c->nz;
+  c->G = p->n_groups, c->M = p->n_mat, c->D = p->n_delayed_max > 0 ? p->n_delayed_max : 0;
+  c->n_ord = p->n_ord;
+  c->scheme = p->scheme, c->mode = p->mode, c->dt = p->dt;
+  DOMA_CUDA(c, cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  c->own_stream = true;
+  DOMA_CUDA(c, cudaEventCreate(&c->ev0));
+  DOMA_CUDA(c, cudaEventCreate(&c->ev1));
+
+  for (int64_t i = 0; i < c->N; ++i)
+    if (p->mat_of_cell[i] < 0 || p->mat_of_cell[i] >= c->M)
+    {
+      snprintf(c->err, DOMA_MAX_ERR, "create: cell %lld has material %d outside [0,%d)", (long long)i, p->mat_of_cell[i], c->M);
+      return 3;
+    }
+  const size_t G = c->G, M = c->M, D = c->D;
+  int rc = 0;
+  std::vector<double> one(1, 1.0);
+  const double * dz_src = p->dims == 3 ? p->dz : one.data();
+#define UP(dst, src, n)                      \
+  if ((rc = upload(c, &c->dst, src, (n)))) \
+    return rc;
+  UP(dx, p->dx, (size_t)c->nx);
+  UP(dy, p->dy, (size_t)c->ny);
+  UP(dz, dz_src, (size_t)c->nz);
+  {
+    std::vector<double> r;
+    r.resize(c->nx);
+    for (int i = 0; i < c->nx; ++i)
+      r[i] = 1.0 / p->dx[i];
+    UP(rdx, r.data(), r.size());
+    r.resize(c->ny);
+    for (int i = 0; i < c->ny; ++i)
+      r[i] = 1.0 / p->dy[i];
+    UP(rdy, r.data(), r.size());
+    r.resize(c->nz);
+    for (int i = 0; i < c->nz; ++i)
+      r[i] = 1.0 / dz_src[i];
+    UP(rdz, r.data(), r.size());
+  }
+  UP(mat, p->mat_of_cell, (size_t)c->N);
+  UP(mat_flags, p->mat_flags, M);
+  UP(n_delayed, p->n_delayed, M);
+  if (p->step_type)
+  {
+    UP(step_type, p->step_type, M);
+  }
+  else if ((rc = upload<int32_t>(c, &c->step_type, nullptr, M, DOMA_STEP_NONE)))
+    return rc;
+  UP(sigma_t, p->sigma_t, M * G);
+  UP(sigma_s, p->sigma_s, M * G * G);
+  UP(nu_sigma_f, p->nu_sigma_f, M * G);
+  UP(chi_p, p->chi_p, M * G);
+  UP(src, p->src, M * G);
+  UP(inv_v, p->inv_v, M * G);
+  UP(chi_d, D ? p->chi_d : nullptr, M * G * D);
+  UP(beta, D ? p->beta : nullptr, M * G * D);
+  UP(lambda, D ? p->lambda : nullptr, M * D);
+  UP(step_t_insert, p->step_t_insert, M);
+  UP(step_t_remove, p->step_t_remove, M);
+  UP(step_src, p->step_src, M * G);
+#undef UP
+  if ((rc = alloc_zero(c, &c->sig_eff, M)))
+    return rc;
+  const size_t N = (size_t)c->N;
+  if ((rc = alloc_zero(c, &c->phi_tot, G * N)) || (rc = alloc_zero(c, &c->phi_prev, G * N)) || (rc = alloc_zero(c, &c->q, N)) ||
+      (rc = alloc_zero(c, &c->phi_cur, N)))
+    return rc;
+  if (c->mode == DOMA_MODE_TRANSIENT)
+  {
+    if ((rc = alloc_zero(c, &c->phi_last, G * N)))
+      return rc;
+    if (D && ((rc = alloc_zero(c, &c->dnp_cur, D * N)) || (rc = alloc_zero(c, &c->dnp_last, D * N))))
+      return rc;
+  }
+  if ((rc = build_units(c, p)))
+    return rc;
+  // face planes per unit, angle fastest
+  const size_t U = c->n_units;
+  c->face_bytes = 0;
+  if (U)
+  {
+    const size_t nfx = U * c->nz * c->ny * 32, nfy = U * c->nz * c->nx * 32, nfz = c->dims == 3 ? U * c->ny * c->nx * 32 : 0;
+    DOMA_CUDA(c, cudaMalloc(&c->face_x, sizeof(double) * nfx));
+    DOMA_CUDA(c, cudaMalloc(&c->face_y, sizeof(double) * nfy));
+    if (nfz)
+      DOMA_CUDA(c, cudaMalloc(&c->face_z, sizeof(double) * nfz));
+    c->face_bytes = sizeof(double) * (nfx + nfy + nfz);
+    c->device_bytes += c->face_bytes;
+  }
+  DOMA_CUDA(c, cudaMalloc(&c->work_counter, sizeof(int)));
+  DOMA_CUDA(c, cudaMalloc(&c->red_partial, sizeof(double) * 2 * 1184));
+  DOMA_CUDA(c, cudaMalloc(&c->red_out, sizeof(double) * 2));
+  DOMA_CUDA(c, cudaMallocHost(&c->h_red, sizeof(double) * 2));
+  c->sweep_variant = 1;
+  // default tile: 8 x 4 x 8 in 3D (8 KB of shared memory per warp), 8 x 4 in 2D
+  int tz = c->dims == 3 ? 8 : 1;
+  if ((rc = doma_sweep_setup_tiles(c, 4, tz)))
+    return rc;
+  return 0;
+}
+
+// ---- NCCL through dlopen: no link-time dependency, the torch-bundled libnccl.so.2 is reused ----
+struct NcclApi
+{
+  void * lib;
+  int (*GetUniqueId)(void *);
+  int (*CommInitRank)(void **, int, char[128], int); // ncclUniqueId is a 128-byte struct passed by value
+  int (*AllReduce)(const void *, void *, size_t, int, int, void *, cudaStream_t);
+  int (*CommDestroy)(void *);
+  const char * (*GetErrorString)(int);
+};
+NcclApi g_nccl = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+
+struct NcclId
+{
+  char b[128];
+};
+
+int
+load_nccl(char * err)
+{
+  if (g_nccl.lib)
+    return 0;
+  const char * names[] = {"libnccl.so.2", "libnccl.so"};
+  for (const char * n : names)
+    if ((g_nccl.lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL)))
+      break;
+  if (!g_nccl.lib)
+  {
+    snprintf(err, DOMA_MAX_ERR, "comm: cannot dlopen libnccl.so.2: %s", dlerror());
+    return 20;
+  }
+  g_nccl.GetUniqueId = (int (*)(void *))dlsym(g_nccl.lib, "ncclGetUniqueId");
+  g_nccl.CommInitRank = (int (*)(void **, int, char[128], int))dlsym(g_nccl.lib, "ncclCommInitRank");
+  g_nccl.AllReduce = (int (*)(const void *, void *, size_t, int, int, void *, cudaStream_t))dlsym(g_nccl.lib, "ncclAllReduce");
+  g_nccl.CommDestroy = (int (*)(void *))dlsym(g_nccl.lib, "ncclCommDestroy");
+  g_nccl.GetErrorString = (const char * (*)(int))dlsym(g_nccl.lib, "ncclGetErrorString");
+  if (!g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.AllReduce || !g_nccl.CommDestroy)
+  {
+    snprintf(err, DOMA_MAX_ERR, "comm: libnccl lacks a required symbol");
+    return 21;
+  }
+  return 0;
+}
+} // namespace
+
+extern "C" {
+
+int
+doma_b200_create(const doma_b200_problem * p, doma_b200_ctx ** out)
+{
+  if (!p || !out || (p->dims != 2 && p->dims != 3) || p->nx < 1 || p->ny < 1 || (p->dims == 3 && p->nz < 1) || p->n_groups < 1 ||
+      p->n_mat < 1 || p->n_ord < 0 || !p->dx || !p->dy || !p->mat_of_cell || !p->sigma_t || !p->sigma_s)
+  {
+    snprintf(g_create_err, DOMA_MAX_ERR, "create: invalid problem description");
+    return 1;
+  }
+  doma_b200_ctx * c = (doma_b200_ctx *)calloc(1, sizeof(doma_b200_ctx));
+  const int rc = create_impl(c, p);
+  if (rc)
+  {
+    memcpy(g_create_err, c->err, DOMA_MAX_ERR);
+    doma_b200_destroy(c);
+    *out = nullptr;
+    return rc;
+  }
+  *out = c;
+  return 0;
+}
+
+int
+doma_b200_destroy(doma_b200_ctx * c)
+{
+  if (!c)
+    return 0;
+  cudaSetDevice(c->device);
+  if (c->stream)
+    cudaStreamSynchronize(c->stream);
+  if (c->nccl_comm && g_nccl.CommDestroy)
+    g_nccl.CommDestroy(c->nccl_comm);
+  void * ptrs[] = {c->dx, c->dy, c->dz, c->rdx, c->rdy, c->rdz, c->mat, c->mat_flags, c->n_delayed, c->step_type, c->sigma_t,
+                   c->sigma_s, c->nu_sigma_f, c->chi_p, c->src, c->inv_v, c->chi_d, c->beta, c->lambda, c->step_t_insert,
+                   c->step_t_remove, c->step_src, c->sig_eff, c->phi_tot, c->phi_prev, c->phi_last, c->dnp_cur, c->dnp_last,
+                   c->q, c->phi_cur, c->unit_octant, c->u_mu, c->u_eta, c->u_xi, c->u_w, c->tile_order, c->face_x, c->face_y,
+                   c->face_z, c->tile_done, c->work_counter, c->red_partial, c->red_out};
+  for (void * p : ptrs)
+    if (p)
+      cudaFree(p);
+  if (c->h_red)
+    cudaFreeHost(c->h_red);
+  if (c->ev0)
+    cudaEventDestroy(c->ev0);
+  if (c->ev1)
+    cudaEventDestroy(c->ev1);
+  if (c->own_stream && c->stream)
+    cudaStreamDestroy(c->stream);
+  free(c->h_units);
+  free(c);
+  return 0;
+}
+
+const char *
+doma_b200_last_error(const doma_b200_ctx * c)
+{
+  return c ? c->err : g_create_err;
+}
+
+int
+doma_b200_set_stream(doma_b200_ctx * c, void * s)
+{
+  DOMA_CUDA(c, cudaStreamSynchronize(c->stream));
+  if (s)
+  {
+    if (c->own_stream)
+      cudaStreamDestroy(c->stream);
+    c->stream = (cudaStream_t)s;
+    c->own_stream = false;
+  }
+  else if (!c->own_stream)
+  {
+    DOMA_CUDA(c, cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    c->own_stream = true;
+  }
+  return 0;
+}
+
+int
+doma_b200_synchronize(doma_b200_ctx * c)
+{
+  DOMA_CUDA(c, cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+#define ENTER(c)                    \
+  if (!(c))                         \
+    return 1;                       \
+  DOMA_CUDA(c, cudaSetDevice((c)->device))
+#define CHECK_GROUP(c, g)                                                             \
+  if ((g) < 0 || (g) >= (c)->G)                                                       \
+  {                                                                                   \
+    snprintf((c)->err, DOMA_MAX_ERR, "%s: group %d outside [0,%d)", __func__, (int)(g), (c)->G); \
+    return 4;                                                                         \
+  }
+
+int doma_b200_reset_state(doma_b200_ctx * c, double phi_init) { ENTER(c); return doma_launch_reset_state(c, phi_init); }
+int doma_b200_init_zero_ic(doma_b200_ctx * c) { ENTER(c); return doma_launch_init_zero_ic(c); }
+int doma_b200_update_step_fluxes(doma_b200_ctx * c) { ENTER(c); return doma_launch_update_step_fluxes(c); }
+int doma_b200_step_dnps(doma_b200_ctx * c) { ENTER(c); return doma_launch_step_dnps(c); }
+
+int
+doma_b200_update_mg_source(doma_b200_ctx * c, int32_t g, double t)
+{
+  ENTER(c);
+  CHECK_GROUP(c, g);
+  return doma_launch_update_mg_source(c, g, t);
+}
+
+int
+doma_b200_update_mg_source_eigen(doma_b200_ctx * c, int32_t g, double k)
+{
+  ENTER(c);
+  CHECK_GROUP(c, g);
+  return doma_launch_update_mg_source_eigen(c, g, k);
+}
+
+int
+doma_b200_update_scatter_source(doma_b200_ctx * c, int32_t g)
+{
+  ENTER(c);
+  CHECK_GROUP(c, g);
+  return doma_launch_update_scatter_source(c, g);
+}
+
+int
+doma_b200_sweep(doma_b200_ctx * c, int32_t g)
+{
+  ENTER(c);
+  CHECK_GROUP(c, g);
+  return doma_launch_sweep(c, g);
+}
+
+// Host-buffer form of sweep(g) for end-to-end timing: q (N doubles, host) -> device, phi_cur = 0,
+// sweep, phi_cur -> host.  Synchronous.
+int
+doma_b200_sweep_from_host(doma_b200_ctx * c, int32_t g, const double * q_host, double * phi_cur_out)
+{
+  ENTER(c);
+  CHECK_GROUP(c, g);
+  DOMA_CUDA(c, cudaMemcpyAsync(c->q, q_host, sizeof(double) * c->N, cudaMemcpyHostToDevice, c->stream));
+  DOMA_CUDA(c, cudaMemsetAsync(c->phi_cur, 0, sizeof(double) * c->N, c->stream));
+  const int rc = doma_launch_sweep(c, g);
+  if (rc)
+    return rc;
+  DOMA_CUDA(c, cudaMemcpyAsync(phi_cur_out, c->phi_cur, sizeof(double) * c->N, cudaMemcpyDeviceToHost, c->stream));
+  DOMA_CUDA(c, cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+int
+doma_b200_scatter_residual(doma_b200_ctx * c, int32_t g, double * out)
+{
+  ENTER(c);
+  CHECK_GROUP(c, g);
+  const int rc = doma_launch_scatter_residual(c, g);
+  if (rc)
+    return rc;
+  // 3D:562: total_L2 > 1e-8 ? sqrt(diff)/sqrt(total) : 0
+  *out = c->h_red[1] > 1e-8 ? sqrt(c->h_red[0]) / sqrt(c->h_red[1]) : 0.0;
+  return 0;
+}
+
+int
+doma_b200_mg_residual(doma_b200_ctx * c, double * out)
+{
+  ENTER(c);
+  const int rc = doma_launch_mg_residual(c);
+  if (rc)
+    return rc;
+  *out = c->h_red[1] > 1e-8 ? sqrt(c->h_red[0]) / sqrt(c->h_red[1]) : 0.0;
+  return 0;
+}
+
+int
+doma_b200_update_k(doma_b200_ctx * c, double * k_inout, double * k_prev_out)
+{
+  ENTER(c);
+  const double k = *k_inout;
+  const int rc = doma_launch_k_sums(c, k);
+  if (rc)
+    return rc;
+  *k_prev_out = k;
+  *k_inout = c->h_red[0] / c->h_red[1];
+  return 0;
+}
+
+static double *
+array_ptr(doma_b200_ctx * c, int which, int index)
+{
+  const int64_t N = c->N;
+  switch (which)
+  {
+    case DOMA_ARR_PHI_TOT: return index >= 0 && index < c->G ? c->phi_tot + index * N : nullptr;
+    case DOMA_ARR_PHI_PREV: return index >= 0 && index < c->G ? c->phi_prev + index * N : nullptr;
+    case DOMA_ARR_PHI_LAST: return c->phi_last && index >= 0 && index < c->G ? c->phi_last + index * N : nullptr;
+    case DOMA_ARR_DNP_CUR: return c->dnp_cur && index >= 0 && index < c->D ? c->dnp_cur + index * N : nullptr;
+    case DOMA_ARR_DNP_LAST: return c->dnp_last && index >= 0 && index < c->D ? c->dnp_last + index * N : nullptr;
+    case DOMA_ARR_Q: return c->q;
+    case DOMA_ARR_PHI_CUR: return c->phi_cur;
+    default: return nullptr;
+  }
+}
+
+int
+doma_b200_get_array(doma_b200_ctx * c, int32_t which, int32_t index, double * host_out)
+{
+  ENTER(c);
+  const double * p = array_ptr(c, which, index);
+  if (!p || !host_out)
+  {
+    snprintf(c->err, DOMA_MAX_ERR, "get_array: no array %d[%d] in this context", which, index);
+    return 4;
+  }
+  DOMA_CUDA(c, cudaMemcpyAsync(host_out, p, sizeof(double) * c->N, cudaMemcpyDeviceToHost, c->stream));
+  DOMA_CUDA(c, cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+int
+doma_b200_set_array(doma_b200_ctx * c, int32_t which, int32_t index, const double * host_in)
+{
+  ENTER(c);
+  double * p = array_ptr(c, which, index);
+  if (!p || !host_in)
+  {
+    snprintf(c->err, DOMA_MAX_ERR, "set_array: no array %d[%d] in this context", which, index);
+    return 4;
+  }
+  DOMA_CUDA(c, cudaMemcpyAsync(p, host_in, sizeof(double) * c->N, cudaMemcpyHostToDevice, c->stream));
+  DOMA_CUDA(c, cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+int
+doma_b200_device_ptr(doma_b200_ctx * c, int32_t which, int32_t index, void ** out)
+{
+  if (!c || !out)
+    return 1;
+  double * p = array_ptr(c, which, index);
+  if (!p)
+  {
+    snprintf(c->err, DOMA_MAX_ERR, "device_ptr: no array %d[%d] in this context", which, index);
+    return 4;
+  }
+  *out = p;
+  return 0;
+}
+
+int
+doma_b200_get_info(doma_b200_ctx * c, int32_t what, int64_t * out)
+{
+  if (!c || !out)
+    return 1;
+  switch (what)
+  {
+    case DOMA_INFO_KERNEL_LAUNCHES: *out = c->launches; break;
+    case DOMA_INFO_SWEEP_VARIANT: *out = c->sweep_variant; break;
+    case DOMA_INFO_N_CELLS: *out = c->N; break;
+    case DOMA_INFO_N_ORD: *out = c->n_ord; break;
+    case DOMA_INFO_FACE_BYTES: *out = c->face_bytes; break;
+    case DOMA_INFO_DEVICE_BYTES: *out = c->device_bytes; break;
+    case DOMA_INFO_N_UNITS: *out = c->n_units; break;
+    case DOMA_INFO_N_TILES: *out = c->n_tiles; break;
+    default: snprintf(c->err, DOMA_MAX_ERR, "get_info: unknown item %d", what); return 4;
+  }
+  return 0;
+}
+
+int
+doma_b200_set_sweep_variant(doma_b200_ctx * c, int32_t variant)
+{
+  if (!c)
+    return 1;
+  if (variant != 1)
+  {
+    snprintf(c->err, DOMA_MAX_ERR, "set_sweep_variant: only variant 1 (persistent KBA tiles) exists");
+    return 4;
+  }
+  c->sweep_variant = variant;
+  return 0;
+}
+
+int
+doma_b200_set_tile(doma_b200_ctx * c, int32_t tx, int32_t ty, int32_t tz)
+{
+  ENTER(c);
+  if (tx != 8)
+  {
+    snprintf(c->err, DOMA_MAX_ERR, "set_tile: the x extent of a tile is fixed to 8 (row held in registers)");
+    return 6;
+  }
+  return doma_sweep_setup_tiles(c, ty, tz);
+}
+
+int
+doma_b200_last_sweep_ms(doma_b200_ctx * c, float * out)
+{
+  ENTER(c);
+  if (!c->have_sweep_time)
+  {
+    *out = 0.f;
+    return 0;
+  }
+  DOMA_CUDA(c, cudaEventSynchronize(c->ev1));
+  DOMA_CUDA(c, cudaEventElapsedTime(out, c->ev0, c->ev1));
+  return 0;
+}
+
+// ---- angle sharding across ranks: one in-place ncclAllReduce(phi_cur) per sweep ----
+int
+doma_b200_comm_unique_id(char * out, int32_t len)
+{
+  if (!out || len < 128)
+    return 1;
+  int rc = load_nccl(g_create_err);
+  if (rc)
+    return rc;
+  NcclId id;
+  const int r = g_nccl.GetUniqueId(&id);
+  if (r)
+  {
+    snprintf(g_create_err, DOMA_MAX_ERR, "ncclGetUniqueId: %s", g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "?");
+    return 22;
+  }
+  memcpy(out, id.b, 128);
+  return 0;
+}
+
+int
+doma_b200_comm_init(doma_b200_ctx * c, int32_t rank, int32_t nranks, const char * unique_id, int32_t len)
+{
+  ENTER(c);
+  if (len < 128 || !unique_id || rank < 0 || rank >= nranks)
+  {
+    snprintf(c->err, DOMA_MAX_ERR, "comm_init: bad arguments");
+    return 1;
+  }
+  int rc = load_nccl(c->err);
+  if (rc)
+    return rc;
+  NcclId id;
+  memcpy(id.b, unique_id, 128);
+  typedef int (*init_fn)(void **, int, NcclId, int);
+  const int r = ((init_fn)g_nccl.CommInitRank)(&c->nccl_comm, nranks, id, rank);
+  if (r)
+  {
+    snprintf(c->err, DOMA_MAX_ERR, "ncclCommInitRank: %s", g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "?");
+    return 23;
+  }
+  c->rank = rank;
+  c->nranks = nranks;
+  return 0;
+}
+
+int
+doma_b200_allreduce_phi_cur(doma_b200_ctx * c)
+{
+  ENTER(c);
+  if (!c->nccl_comm)
+    return 0; // single rank
+  const int r = g_nccl.AllReduce(c->phi_cur, c->phi_cur, (size_t)c->N, /*ncclDouble*/ 8, /*ncclSum*/ 0, c->nccl_comm, c->stream);
+  if (r)
+  {
+    snprintf(c->err, DOMA_MAX_ERR, "ncclAllReduce: %s", g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "?");
+    return 24;
+  }
+  c->launches += 1;
+  return 0;
+}
+
+} // extern "C"

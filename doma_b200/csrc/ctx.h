@@ -1,0 +1,110 @@
+// ctx.h — device-resident problem state shared by the translation units of libdoma_b200.so.
+//
+// Data layout in HBM (structure of arrays, x-fastest like the reference's cell index
+// k*ny*nx + j*nx + i, src/BrickMesh3D.cpp:86-102) replacing the reference's 256-byte
+// CartesianCell3D objects with five heap vectors each (include/CartesianCell3D.h:84-121):
+//   q[N], phi_cur[N]                       _current_iteration_source, _current_scalar_flux
+//   phi_tot[G][N], phi_prev[G][N]          _total_scalar_flux[g], _prev_mg_scalar_flux[g]
+//   phi_last[G][N], dnp_cur/last[D][N]     transient mode only
+//   mat[N] (int32 dense material index), dx[nx] dy[ny] dz[nz] and their reciprocals
+//   material tables [M][G] / [M][G][G] / [M][G][D]
+//   sweep scratch: per (octant, angle-batch) "unit" three face planes, angle fastest (32 lanes),
+//   tile-done flags, the hyperplane-ordered tile table and the work-queue counter.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "doma_b200.h"
+
+#define DOMA_MAX_ERR 512
+#define DOMA_LANES 32  // ordinates of one octant batched across the lanes of a warp
+
+struct SweepUnit
+{
+  int octant;  // DOMA_OCT_*
+  int n_lanes; // active lanes (ordinates) in this unit, <= 32
+};
+
+struct doma_b200_ctx
+{
+  int device;
+  int dims, nx, ny, nz, G, M, D, n_ord, scheme, mode;
+  int64_t N;
+  double dt;
+  cudaStream_t stream;
+  bool own_stream;
+  int n_sms;
+
+  // geometry / materials
+  double *dx, *dy, *dz, *rdx, *rdy, *rdz;
+  int32_t * mat;
+  int32_t *mat_flags, *n_delayed, *step_type;
+  double *sigma_t, *sigma_s, *nu_sigma_f, *chi_p, *src, *inv_v, *chi_d, *beta, *lambda;
+  double *step_t_insert, *step_t_remove, *step_src;
+  double * sig_eff; // [M] total cross section the cell solve uses for the group being swept
+
+  // state
+  double *phi_tot, *phi_prev, *phi_last, *dnp_cur, *dnp_last, *q, *phi_cur;
+
+  // quadrature, regrouped into sweep units (octant x batch of <=32 ordinates), lane-major
+  int n_units;
+  SweepUnit * h_units; // host copy
+  int * unit_octant;   // [U]
+  double *u_mu, *u_eta, *u_xi, *u_w; // [U][32] absolute direction cosines; padding lanes: 1,1,1,w=0
+
+  // sweep scratch
+  int tile_x, tile_y, tile_z; // tile_x is fixed to 8 by the kernel (row held in registers)
+  int ntx, nty, ntz, n_tiles;
+  uint32_t * tile_order; // [n_tiles] packed (I',J',K') sorted by I'+J'+K'
+  double *face_x, *face_y, *face_z; // [U][nz][ny][32], [U][nz][nx][32], [U][ny][nx][32]
+  int * tile_done;                   // [U][n_tiles] epoch of completion
+  int * work_counter;                // [1]
+  int epoch;
+  int sweep_variant;
+  int64_t face_bytes, device_bytes;
+
+  // reductions
+  double * red_partial; // [2 * RED_BLOCKS]
+  double * red_out;     // [2] device
+  double * h_red;       // [2] pinned host
+
+  // timing / accounting
+  cudaEvent_t ev0, ev1;
+  bool have_sweep_time;
+  int64_t launches;
+
+  // NCCL (resolved with dlopen at comm_init; see api.cu)
+  void * nccl_comm;
+  int rank, nranks;
+
+  char err[DOMA_MAX_ERR];
+};
+
+#define DOMA_CUDA(ctx, call)                                                                                     \
+  do                                                                                                             \
+  {                                                                                                              \
+    cudaError_t e_ = (call);                                                                                     \
+    if (e_ != cudaSuccess)                                                                                       \
+    {                                                                                                            \
+      snprintf((ctx)->err, DOMA_MAX_ERR, "%s:%d: %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); \
+      return 100 + (int)e_;                                                                                      \
+    }                                                                                                            \
+  } while (0)
+
+// elementwise.cu
+int doma_launch_reset_state(doma_b200_ctx * c, double phi_init);
+int doma_launch_init_zero_ic(doma_b200_ctx * c);
+int doma_launch_update_step_fluxes(doma_b200_ctx * c);
+int doma_launch_step_dnps(doma_b200_ctx * c);
+int doma_launch_update_mg_source(doma_b200_ctx * c, int g, double t);
+int doma_launch_update_mg_source_eigen(doma_b200_ctx * c, int g, double k);
+int doma_launch_update_scatter_source(doma_b200_ctx * c, int g);
+int doma_launch_scatter_residual(doma_b200_ctx * c, int g); // leaves (diff, total) in h_red after sync
+int doma_launch_mg_residual(doma_b200_ctx * c);
+int doma_launch_k_sums(doma_b200_ctx * c, double k);
+int doma_launch_sig_eff(doma_b200_ctx * c, int g);
+
+// sweep.cu
+int doma_sweep_setup_tiles(doma_b200_ctx * c, int ty, int tz);
+int doma_launch_sweep(doma_b200_ctx * c, int g);

@@ -1,0 +1,439 @@
+// elementwise.cu — source build, state management and reduction kernels (FP64 CUDA cores, HBM-bound).
+//
+// One thread per cell, structure-of-arrays, coalesced along x.  This translation unit is compiled
+// with -fmad=false and every expression keeps the reference's operation order, so the per-cell
+// values are bit-identical to the reference's (g++ -O2 on x86-64 does not contract to FMA,
+// SURVEY Appendix A); only the order of the two-stage reductions differs (fixed, deterministic).
+// Citations: "3D" = src/TransportSolver3D.cpp of the DOMA tree (2D twin: same lines of
+// src/TransportSolver2D.cpp with 0.5 instead of 0.25 and _area instead of _volume).
+#include "ctx.h"
+
+#include <math.h>
+
+#ifndef M_PI
+#define M_PI 3.14159265358979323846
+#endif
+
+namespace
+{
+constexpr int EW_THREADS = 256;
+constexpr int RED_BLOCKS = 1184; // 148 SMs x 8 resident blocks of 256 threads
+
+inline int
+ew_blocks(int64_t n)
+{
+  return (int)((n + EW_THREADS - 1) / EW_THREADS);
+}
+
+struct Geo
+{
+  const double *dx, *dy, *dz;
+  int nx, ny, dims;
+  // CartesianCell3D::_volume = l_x*l_y*l_z (src/CartesianCell3D.cpp:19); 2D: _area = l_x*l_y
+  __device__ double measure(int64_t id) const
+  {
+    const int i = (int)(id % nx);
+    const int64_t r = id / nx;
+    const int j = (int)(r % ny);
+    const int k = (int)(r / ny);
+    return dims == 3 ? dx[i] * dy[j] * dz[k] : dx[i] * dy[j];
+  }
+};
+
+Geo
+geo_of(const doma_b200_ctx * c)
+{
+  return Geo{c->dx, c->dy, c->dz, c->nx, c->ny, c->dims};
+}
+
+__global__ void
+fill_kernel(double * __restrict__ p, int64_t n, double v)
+{
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n)
+    p[i] = v;
+}
+
+// stepDNPs (3D:236-260)
+__global__ void
+step_dnps_kernel(int64_t N, int G, int D, double dt, const int32_t * __restrict__ mat, const int32_t * __restrict__ n_delayed,
+                 const double * __restrict__ nu_sigma_f, const double * __restrict__ beta, const double * __restrict__ lambda,
+                 const double * __restrict__ phi_tot, double * __restrict__ dnp_cur, double * __restrict__ dnp_last)
+{
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= N)
+    return;
+  const int m = mat[i];
+  const int nd = n_delayed[m];
+  for (int d = 0; d < nd; ++d)
+  {
+    double c_src = 0.0;
+    for (int g = 0; g < G; ++g)
+      c_src += nu_sigma_f[m * G + g] * phi_tot[g * N + i] * beta[(m * G + g) * D + d];
+    const double lam = lambda[m * D + d];
+    const double decay = exp(-lam * dt);
+    const double v = (c_src / lam) * (1.0 - decay) + dnp_last[d * N + i] * decay;
+    dnp_cur[d * N + i] = v;
+    dnp_last[d * N + i] = v;
+  }
+}
+
+// updateMultigroupSource(g,t) (3D:339-402)
+__global__ void
+mg_source_kernel(int64_t N, int G, int D, int g, double t, double f, int transient, double dt,
+                 const int32_t * __restrict__ mat, const int32_t * __restrict__ mat_flags,
+                 const int32_t * __restrict__ n_delayed, const int32_t * __restrict__ step_type,
+                 const double * __restrict__ step_t_insert, const double * __restrict__ step_t_remove,
+                 const double * __restrict__ step_src, const double * __restrict__ src, const double * __restrict__ sigma_s,
+                 const double * __restrict__ chi_p, const double * __restrict__ nu_sigma_f, const double * __restrict__ beta,
+                 const double * __restrict__ chi_d, const double * __restrict__ lambda, const double * __restrict__ inv_v,
+                 const double * __restrict__ dnp_cur, const double * __restrict__ phi_last, double * __restrict__ phi_tot,
+                 double * __restrict__ phi_prev, double * __restrict__ q_out, double * __restrict__ phi_cur)
+{
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= N)
+    return;
+  const int m = mat[i];
+  const int nd = n_delayed[m];
+  const bool has_chi = (mat_flags[m] & DOMA_MAT_HAS_CHI_P) != 0;
+  phi_cur[i] = 0.0;
+  double q = (mat_flags[m] & DOMA_MAT_HAS_SRC) ? f * src[m * G + g] / M_PI : 0.0;
+  if (transient && step_type[m] != DOMA_STEP_NONE)
+  {
+    const double s = f * step_src[m * G + g] / M_PI;
+    switch (step_type[m])
+    {
+      case DOMA_STEP_BOTH: q += (step_t_insert[m] <= t && t <= step_t_remove[m]) ? s : 0.0; break;
+      case DOMA_STEP_INSERT: q += (step_t_insert[m] <= t) ? s : 0.0; break;
+      case DOMA_STEP_REMOVE: q += (t <= step_t_remove[m]) ? s : 0.0; break;
+      default: break;
+    }
+  }
+  for (int gp = 0; gp < G; ++gp)
+  {
+    const double phi = phi_tot[gp * N + i];
+    if (gp != g)
+      q += f * sigma_s[(m * G + g) * G + gp] * phi / M_PI;
+    if (has_chi && nd == 0)
+      q += f * chi_p[m * G + g] * nu_sigma_f[m * G + gp] * phi / M_PI;
+    else if (has_chi && nd > 0)
+    {
+      double g_beta = 0.0;
+      for (int d = 0; d < nd; ++d)
+        g_beta += beta[(m * G + gp) * D + d];
+      q += f * (1.0 - g_beta) * chi_p[m * G + g] * nu_sigma_f[m * G + gp] * phi / M_PI;
+    }
+    // these two terms sit inside the g' loop of the reference -> added G times
+    if (nd > 0 && transient)
+      for (int d = 0; d < nd; ++d)
+        q += f * chi_d[(m * G + g) * D + d] * dnp_cur[d * N + i] * lambda[m * D + d] / M_PI;
+    if (transient)
+      q += f * phi_last[g * N + i] * inv_v[m * G + g] / dt / M_PI;
+  }
+  q_out[i] = q;
+  phi_prev[g * N + i] = phi_tot[g * N + i];
+  phi_tot[g * N + i] = 0.0;
+}
+
+// updateMultigroupSourceEigen(g) (3D:404-430): "+=" onto the stale q
+__global__ void
+mg_source_eigen_kernel(int64_t N, int G, int g, double k, double f, const int32_t * __restrict__ mat,
+                       const int32_t * __restrict__ mat_flags, const double * __restrict__ sigma_s,
+                       const double * __restrict__ chi_p, const double * __restrict__ nu_sigma_f,
+                       double * __restrict__ phi_tot, double * __restrict__ phi_prev, double * __restrict__ q_io,
+                       double * __restrict__ phi_cur)
+{
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= N)
+    return;
+  const int m = mat[i];
+  const bool has_chi = (mat_flags[m] & DOMA_MAT_HAS_CHI_P) != 0;
+  phi_cur[i] = 0.0;
+  double q = q_io[i];
+  for (int gp = 0; gp < G; ++gp)
+  {
+    const double phi = phi_tot[gp * N + i];
+    if (gp != g)
+      q += f * sigma_s[(m * G + g) * G + gp] * phi / M_PI;
+    if (has_chi)
+      q += f * chi_p[m * G + g] * nu_sigma_f[m * G + gp] * phi / M_PI / k;
+  }
+  q_io[i] = q;
+  phi_prev[g * N + i] = phi_tot[g * N + i];
+  phi_tot[g * N + i] = 0.0;
+}
+
+// updateScatteringSource(g) (3D:531-545)
+__global__ void
+scatter_source_kernel(int64_t N, int G, int g, double f, const int32_t * __restrict__ mat,
+                      const double * __restrict__ sigma_s, double * __restrict__ phi_tot_g, double * __restrict__ q,
+                      double * __restrict__ phi_cur)
+{
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= N)
+    return;
+  const int m = mat[i];
+  const double cur = phi_cur[i];
+  phi_tot_g[i] += cur;
+  q[i] = f * sigma_s[(m * G + g) * G + g] * cur / M_PI;
+  phi_cur[i] = 0.0;
+}
+
+// total cross section seen by the cell solve for group g: sigma_t, plus inv_v/dt for 2D transients
+// (the 3D sweeps never pass mode/dt to the cell solve)
+__global__ void
+sig_eff_kernel(int M, int G, int g, int add_inv_v, double dt, const double * __restrict__ sigma_t,
+               const double * __restrict__ inv_v, double * __restrict__ sig_eff)
+{
+  const int m = blockIdx.x * blockDim.x + threadIdx.x;
+  if (m >= M)
+    return;
+  double tot = sigma_t[m * G + g];
+  if (add_inv_v)
+    tot += inv_v[m * G + g] / dt;
+  sig_eff[m] = tot;
+}
+
+// ---- reductions: block partials in a fixed grid, then one block sums the partials in order ----
+__device__ void
+block_reduce2(double a, double b, double * __restrict__ partial, int slot)
+{
+  __shared__ double sa[EW_THREADS / 32], sb[EW_THREADS / 32];
+  for (int o = 16; o > 0; o >>= 1)
+  {
+    a += __shfl_down_sync(0xffffffffu, a, o);
+    b += __shfl_down_sync(0xffffffffu, b, o);
+  }
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  if (lane == 0)
+  {
+    sa[w] = a;
+    sb[w] = b;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0)
+  {
+    double ta = 0.0, tb = 0.0;
+    for (int i = 0; i < EW_THREADS / 32; ++i)
+    {
+      ta += sa[i];
+      tb += sb[i];
+    }
+    partial[slot] = ta;
+    partial[RED_BLOCKS + slot] = tb;
+  }
+}
+
+// computeScatteringResidual(g) (3D:547-563): sum V*cur^2, sum V*(tot+cur)^2
+__global__ void
+scatter_residual_kernel(int64_t N, Geo geo, const double * __restrict__ phi_tot_g, const double * __restrict__ phi_cur,
+                        double * __restrict__ partial)
+{
+  double diff = 0.0, total = 0.0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < N; i += (int64_t)gridDim.x * blockDim.x)
+  {
+    const double v = geo.measure(i);
+    const double cur = phi_cur[i], s = phi_tot_g[i] + cur;
+    diff = diff + (cur * cur) * v;
+    total = total + (s * s) * v;
+  }
+  block_reduce2(diff, total, partial, blockIdx.x);
+}
+
+// computeMGFluxResidual() (3D:318-337)
+__global__ void
+mg_residual_kernel(int64_t N, int G, Geo geo, const double * __restrict__ phi_tot, const double * __restrict__ phi_prev,
+                   double * __restrict__ partial)
+{
+  double diff = 0.0, total = 0.0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < N; i += (int64_t)gridDim.x * blockDim.x)
+  {
+    const double v = geo.measure(i);
+    for (int g = 0; g < G; ++g)
+    {
+      const double s = phi_tot[g * N + i], d = s - phi_prev[g * N + i];
+      diff = diff + (d * d) * v;
+      total = total + (s * s) * v;
+    }
+  }
+  block_reduce2(diff, total, partial, blockIdx.x);
+}
+
+// updateEigenvalue() (3D:432-456): num = sum V nuSf phi_tot, den = sum V nuSf phi_prev / k
+__global__ void
+k_sums_kernel(int64_t N, int G, double k, Geo geo, const int32_t * __restrict__ mat, const int32_t * __restrict__ mat_flags,
+              const double * __restrict__ nu_sigma_f, const double * __restrict__ phi_tot,
+              const double * __restrict__ phi_prev, double * __restrict__ partial)
+{
+  double num = 0.0, den = 0.0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < N; i += (int64_t)gridDim.x * blockDim.x)
+  {
+    const int m = mat[i];
+    if (!(mat_flags[m] & DOMA_MAT_HAS_NU_SIGMA_F))
+      continue;
+    const double v = geo.measure(i);
+    for (int g = 0; g < G; ++g)
+    {
+      num = num + v * nu_sigma_f[m * G + g] * phi_tot[g * N + i];
+      den = den + v * nu_sigma_f[m * G + g] * phi_prev[g * N + i] / k;
+    }
+  }
+  block_reduce2(num, den, partial, blockIdx.x);
+}
+
+__global__ void
+final_reduce_kernel(const double * __restrict__ partial, double * __restrict__ out)
+{
+  // 2 warps: warp 0 sums the first RED_BLOCKS partials, warp 1 the second; lane-strided then a
+  // fixed shuffle tree -> deterministic
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  double a = 0.0;
+  for (int i = lane; i < RED_BLOCKS; i += 32)
+    a += partial[w * RED_BLOCKS + i];
+  for (int o = 16; o > 0; o >>= 1)
+    a += __shfl_down_sync(0xffffffffu, a, o);
+  if (lane == 0)
+    out[w] = a;
+}
+
+int
+finish_reduce(doma_b200_ctx * c)
+{
+  final_reduce_kernel<<<1, 64, 0, c->stream>>>(c->red_partial, c->red_out);
+  c->launches += 2;
+  DOMA_CUDA(c, cudaGetLastError());
+  DOMA_CUDA(c, cudaMemcpyAsync(c->h_red, c->red_out, 2 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  DOMA_CUDA(c, cudaStreamSynchronize(c->stream));
+  return 0;
+}
+} // namespace
+
+int
+doma_launch_reset_state(doma_b200_ctx * c, double phi_init)
+{
+  const int64_t GN = (int64_t)c->G * c->N;
+  fill_kernel<<<ew_blocks(GN), EW_THREADS, 0, c->stream>>>(c->phi_tot, GN, phi_init);
+  c->launches += 1;
+  DOMA_CUDA(c, cudaGetLastError());
+  DOMA_CUDA(c, cudaMemsetAsync(c->phi_prev, 0, sizeof(double) * GN, c->stream));
+  DOMA_CUDA(c, cudaMemsetAsync(c->q, 0, sizeof(double) * c->N, c->stream));
+  DOMA_CUDA(c, cudaMemsetAsync(c->phi_cur, 0, sizeof(double) * c->N, c->stream));
+  return 0;
+}
+
+int
+doma_launch_init_zero_ic(doma_b200_ctx * c)
+{
+  const int64_t GN = (int64_t)c->G * c->N;
+  DOMA_CUDA(c, cudaMemsetAsync(c->phi_tot, 0, sizeof(double) * GN, c->stream));
+  DOMA_CUDA(c, cudaMemsetAsync(c->phi_prev, 0, sizeof(double) * GN, c->stream));
+  if (c->phi_last)
+    DOMA_CUDA(c, cudaMemsetAsync(c->phi_last, 0, sizeof(double) * GN, c->stream));
+  if (c->dnp_cur)
+  {
+    DOMA_CUDA(c, cudaMemsetAsync(c->dnp_cur, 0, sizeof(double) * c->D * c->N, c->stream));
+    DOMA_CUDA(c, cudaMemsetAsync(c->dnp_last, 0, sizeof(double) * c->D * c->N, c->stream));
+  }
+  return 0;
+}
+
+int
+doma_launch_update_step_fluxes(doma_b200_ctx * c)
+{
+  const int64_t GN = (int64_t)c->G * c->N;
+  if (!c->phi_last)
+  {
+    snprintf(c->err, DOMA_MAX_ERR, "update_step_fluxes: context was not created in transient mode");
+    return 5;
+  }
+  DOMA_CUDA(c, cudaMemcpyAsync(c->phi_last, c->phi_tot, sizeof(double) * GN, cudaMemcpyDeviceToDevice, c->stream));
+  DOMA_CUDA(c, cudaMemsetAsync(c->phi_tot, 0, sizeof(double) * GN, c->stream));
+  DOMA_CUDA(c, cudaMemsetAsync(c->q, 0, sizeof(double) * c->N, c->stream));
+  DOMA_CUDA(c, cudaMemsetAsync(c->phi_cur, 0, sizeof(double) * c->N, c->stream));
+  return 0;
+}
+
+int
+doma_launch_step_dnps(doma_b200_ctx * c)
+{
+  if (c->D == 0 || !c->dnp_cur)
+    return 0;
+  step_dnps_kernel<<<ew_blocks(c->N), EW_THREADS, 0, c->stream>>>(c->N, c->G, c->D, c->dt, c->mat, c->n_delayed, c->nu_sigma_f,
+                                                                  c->beta, c->lambda, c->phi_tot, c->dnp_cur, c->dnp_last);
+  c->launches += 1;
+  DOMA_CUDA(c, cudaGetLastError());
+  return 0;
+}
+
+int
+doma_launch_update_mg_source(doma_b200_ctx * c, int g, double t)
+{
+  const double f = c->dims == 3 ? 0.25 : 0.5;
+  const int transient = c->mode == DOMA_MODE_TRANSIENT;
+  mg_source_kernel<<<ew_blocks(c->N), EW_THREADS, 0, c->stream>>>(
+      c->N, c->G, c->D, g, t, f, transient, c->dt, c->mat, c->mat_flags, c->n_delayed, c->step_type, c->step_t_insert,
+      c->step_t_remove, c->step_src, c->src, c->sigma_s, c->chi_p, c->nu_sigma_f, c->beta, c->chi_d, c->lambda, c->inv_v,
+      c->dnp_cur, c->phi_last, c->phi_tot, c->phi_prev, c->q, c->phi_cur);
+  c->launches += 1;
+  DOMA_CUDA(c, cudaGetLastError());
+  return 0;
+}
+
+int
+doma_launch_update_mg_source_eigen(doma_b200_ctx * c, int g, double k)
+{
+  const double f = c->dims == 3 ? 0.25 : 0.5;
+  mg_source_eigen_kernel<<<ew_blocks(c->N), EW_THREADS, 0, c->stream>>>(c->N, c->G, g, k, f, c->mat, c->mat_flags, c->sigma_s,
+                                                                        c->chi_p, c->nu_sigma_f, c->phi_tot, c->phi_prev, c->q,
+                                                                        c->phi_cur);
+  c->launches += 1;
+  DOMA_CUDA(c, cudaGetLastError());
+  return 0;
+}
+
+int
+doma_launch_update_scatter_source(doma_b200_ctx * c, int g)
+{
+  const double f = c->dims == 3 ? 0.25 : 0.5;
+  scatter_source_kernel<<<ew_blocks(c->N), EW_THREADS, 0, c->stream>>>(c->N, c->G, g, f, c->mat, c->sigma_s,
+                                                                       c->phi_tot + (int64_t)g * c->N, c->q, c->phi_cur);
+  c->launches += 1;
+  DOMA_CUDA(c, cudaGetLastError());
+  return 0;
+}
+
+int
+doma_launch_scatter_residual(doma_b200_ctx * c, int g)
+{
+  scatter_residual_kernel<<<RED_BLOCKS, EW_THREADS, 0, c->stream>>>(c->N, geo_of(c), c->phi_tot + (int64_t)g * c->N, c->phi_cur,
+                                                                    c->red_partial);
+  DOMA_CUDA(c, cudaGetLastError());
+  return finish_reduce(c);
+}
+
+int
+doma_launch_mg_residual(doma_b200_ctx * c)
+{
+  mg_residual_kernel<<<RED_BLOCKS, EW_THREADS, 0, c->stream>>>(c->N, c->G, geo_of(c), c->phi_tot, c->phi_prev, c->red_partial);
+  DOMA_CUDA(c, cudaGetLastError());
+  return finish_reduce(c);
+}
+
+int
+doma_launch_k_sums(doma_b200_ctx * c, double k)
+{
+  k_sums_kernel<<<RED_BLOCKS, EW_THREADS, 0, c->stream>>>(c->N, c->G, k, geo_of(c), c->mat, c->mat_flags, c->nu_sigma_f,
+                                                          c->phi_tot, c->phi_prev, c->red_partial);
+  DOMA_CUDA(c, cudaGetLastError());
+  return finish_reduce(c);
+}
+
+int
+doma_launch_sig_eff(doma_b200_ctx * c, int g)
+{
+  const int add = (c->dims == 2 && c->mode == DOMA_MODE_TRANSIENT) ? 1 : 0;
+  sig_eff_kernel<<<(c->M + 63) / 64, 64, 0, c->stream>>>(c->M, c->G, g, add, c->dt, c->sigma_t, c->inv_v, c->sig_eff);
+  c->launches += 1;
+  DOMA_CUDA(c, cudaGetLastError());
+  return 0;
+}

@@ -117,6 +117,18 @@ int doma_b200_update_scatter_source(doma_b200_ctx * ctx, int32_t g);
  * (doma_b200_device_ptr(DOMA_PTR_PHI_CUR) + an all-reduce on the same stream). */
 int doma_b200_sweep(doma_b200_ctx * ctx, int32_t g);
 
+/* Host-buffer form of sweep(g), the call a host-resident driver makes: copies q (N doubles, reference
+ * cell order) to the device, zeroes phi_cur, sweeps, copies phi_cur back into phi_cur_out. Synchronous. */
+int doma_b200_sweep_from_host(doma_b200_ctx * ctx, int32_t g, const double * q_host, double * phi_cur_out);
+
+/* angle sharding across ranks (one process per GPU): the scalar-flux increment is summed once per
+ * sweep with an in-place ncclAllReduce(phi_cur, N, ncclDouble, ncclSum) on the context's stream
+ * (replaces the serial thread-sum of 3D:609-621).  Rank 0 creates the 128-byte NCCL unique id, the
+ * host layer distributes it, every rank calls comm_init once.  Without comm_init, allreduce is a no-op. */
+int doma_b200_comm_unique_id(char * out128, int32_t len);
+int doma_b200_comm_init(doma_b200_ctx * ctx, int32_t rank, int32_t nranks, const char * unique_id128, int32_t len);
+int doma_b200_allreduce_phi_cur(doma_b200_ctx * ctx);
+
 /* reductions (each synchronises and returns scalars) ------------------------------------------- */
 /* computeScatteringResidual(g) (3D:547-563) */
 int doma_b200_scatter_residual(doma_b200_ctx * ctx, int32_t g, double * out);
@@ -146,15 +158,19 @@ int doma_b200_device_ptr(doma_b200_ctx * ctx, int32_t which, int32_t index, void
 enum
 {
   DOMA_INFO_KERNEL_LAUNCHES = 0, /* kernels launched by this context so far */
-  DOMA_INFO_SWEEP_VARIANT = 1,   /* 0 = hyperplane-per-launch, 1 = persistent KBA tiles */
+  DOMA_INFO_SWEEP_VARIANT = 1,   /* 1 = persistent KBA tiles (the only variant so far) */
   DOMA_INFO_N_CELLS = 2,
   DOMA_INFO_N_ORD = 3,
   DOMA_INFO_FACE_BYTES = 4,
-  DOMA_INFO_DEVICE_BYTES = 5
+  DOMA_INFO_DEVICE_BYTES = 5,
+  DOMA_INFO_N_UNITS = 6,         /* sweep units = (octant, batch of <= 32 ordinates) */
+  DOMA_INFO_N_TILES = 7          /* tiles of the KBA decomposition */
 };
 int doma_b200_get_info(doma_b200_ctx * ctx, int32_t what, int64_t * out);
 /* select the sweep implementation (see DOMA_INFO_SWEEP_VARIANT); default 1 */
 int doma_b200_set_sweep_variant(doma_b200_ctx * ctx, int32_t variant);
+/* KBA tile extents in cells; tx must be 8 (the row a warp keeps in registers). Rebuilds the tile table. */
+int doma_b200_set_tile(doma_b200_ctx * ctx, int32_t tx, int32_t ty, int32_t tz);
 /* device time in ms of the most recent doma_b200_sweep (CUDA events on the context's stream; synchronises) */
 int doma_b200_last_sweep_ms(doma_b200_ctx * ctx, float * out);
 

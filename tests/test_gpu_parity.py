@@ -1,0 +1,177 @@
+"""GPU parity tests proper: the CUDA path (through the C ABI) against the CPU oracle on the same
+seeded inputs and against the golden fixtures the unmodified reference produced.
+
+Tolerances (BASELINE.json north_star): scalar flux <= 1e-10 relative, k_eff <= 1e-9, identical
+source-iteration traces.  The per-cell elementwise kernels are compiled without FMA contraction
+and must be bit-identical; reductions may differ by summation order only.
+"""
+import numpy as np
+import pytest
+
+from conftest import golden_case_path, golden_names, load_golden
+
+import doma_b200 as d
+from doma_b200 import abi
+from doma_b200.synthetic import random_problem, synthetic_case
+
+pytestmark = pytest.mark.gpu
+
+FLUX_RTOL = 1e-10
+K_TOL = 1e-9
+
+
+def relmax(a, b):
+    return float(np.max(np.abs(a - b) / np.maximum(np.abs(b), 1e-300)))
+
+
+def solve(name, lib):
+    params, prob = d.load_case(golden_case_path(name))
+    ctx = abi.Context(prob, lib)
+    s = d.TransportSolver(ctx, params)
+    ok = s.solve()
+    return params, prob, ctx, s, ok
+
+
+@pytest.mark.parametrize("name", golden_names())
+def test_cuda_matches_reference_golden(name, cuda_lib):
+    g = load_golden(name)
+    params, prob, ctx, s, ok = solve(name, cuda_lib)
+    assert ok == bool(g["ok"])
+    assert list(s.trace.si_counts) == list(g["si_counts"]), "source-iteration trace differs from the reference"
+    phi = s.flux()
+    assert relmax(phi, g["phi"]) <= FLUX_RTOL
+    np.testing.assert_allclose(np.array(s.trace.si_residuals), g["si_residuals"], rtol=1e-9, atol=0)
+    if params.mode == abi.MODE_EIGEN:
+        assert abs(s.k - float(g["k"])) <= K_TOL
+    if params.mode == abi.MODE_TRANSIENT and prob.n_delayed_max:
+        dnp = np.stack([ctx.get_array(abi.ARR_DNP_CUR, i) for i in range(prob.n_delayed_max)])
+        assert relmax(dnp, g["dnp"]) <= FLUX_RTOL
+    assert ctx.info(abi.INFO_KERNEL_LAUNCHES) > 0
+
+
+SHAPES = [  # (shape, dims, scheme, npol, nazi, tile) incl. ragged tiles and lane counts 1..32+
+    ((13, 7, 5), 3, 1, 2, 2, (4, 8)),
+    ((8, 4, 8), 3, 1, 1, 1, (4, 8)),
+    ((1, 1, 1), 3, 1, 1, 1, (4, 8)),
+    ((33, 17, 9), 3, 1, 5, 5, (4, 4)),
+    ((20, 20, 20), 3, 0, 3, 3, (2, 3)),
+    ((24, 9, 31), 3, 1, 3, 4, (8, 2)),
+    ((19, 23, 1), 2, 1, 3, 3, (4, 1)),
+    ((40, 37, 1), 2, 0, 2, 5, (2, 1)),
+    ((1, 5, 1), 2, 1, 1, 1, (4, 1)),
+]
+
+
+@pytest.mark.parametrize("shape,dims,scheme,npol,nazi,tile", SHAPES)
+def test_single_sweep_matches_oracle(shape, dims, scheme, npol, nazi, tile, cuda_lib, oracle_lib):
+    mode = abi.MODE_TRANSIENT if dims == 2 else abi.MODE_FIXED
+    prob = random_problem(shape, G=2, dims=dims, scheme=scheme, npol=npol, nazi=nazi, seed=sum(shape), mode=mode, dt=0.01)
+    rng = np.random.default_rng(1)
+    # sources spanning many decades so both branches of the 1e-8 switch are taken
+    q = 10.0 ** rng.uniform(-12, 2, prob.n_cells) * (rng.random(prob.n_cells) > 0.2)
+    out = []
+    for lib in (oracle_lib, cuda_lib):
+        ctx = abi.Context(prob, lib)
+        if lib is cuda_lib:
+            ctx.set_tile(8, *tile)
+        ctx.reset_state(0.0)
+        ctx.set_array(abi.ARR_Q, 0, q)
+        for g in (1, 1):           # two sweeps into the same phi_cur: accumulation and epoch reuse
+            ctx.sweep(g)
+        out.append(ctx.get_array(abi.ARR_PHI_CUR, 0))
+    assert np.all(out[0] > 0) or np.any(q == 0)
+    assert relmax(out[1], out[0]) <= FLUX_RTOL
+
+
+def test_sweep_from_host_equals_resident(cuda_lib):
+    prob = random_problem((17, 9, 6), G=1, seed=5)
+    q = np.random.default_rng(2).uniform(0, 1, prob.n_cells)
+    ctx = abi.Context(prob, cuda_lib)
+    ctx.reset_state(0.0)
+    ctx.set_array(abi.ARR_Q, 0, q)
+    ctx.sweep(0)
+    a = ctx.get_array(abi.ARR_PHI_CUR, 0)
+    b = np.empty_like(a)
+    ctx.sweep_from_host(0, q, b)
+    assert relmax(b, a) <= 1e-13
+
+
+def test_elementwise_kernels_bit_identical(cuda_lib, oracle_lib):
+    """Source build / update / DNP step: same per-cell arithmetic, no FMA -> identical bits."""
+    for dims, mode, D in ((3, abi.MODE_FIXED, 0), (3, abi.MODE_EIGEN, 0), (2, abi.MODE_TRANSIENT, 3), (3, abi.MODE_TRANSIENT, 2)):
+        shape = (11, 6, 4) if dims == 3 else (15, 9, 1)
+        prob = random_problem(shape, G=3, dims=dims, mode=mode, D=D, dt=0.02, seed=dims * 10 + mode)
+        prob.step_type[1] = abi.STEP_BOTH
+        prob.step_t_remove[1] = 0.5
+        prob.step_src[1] = [3.0, 0.0, 1.0]
+        rng = np.random.default_rng(3)
+        N, G = prob.n_cells, 3
+        state = {(abi.ARR_PHI_TOT, g): rng.uniform(0, 5, N) for g in range(G)}
+        state.update({(abi.ARR_PHI_PREV, g): rng.uniform(0, 5, N) for g in range(G)})
+        state[(abi.ARR_Q, 0)] = rng.uniform(0, 1, N)
+        state[(abi.ARR_PHI_CUR, 0)] = rng.uniform(0, 1, N)
+        if mode == abi.MODE_TRANSIENT:
+            state.update({(abi.ARR_PHI_LAST, g): rng.uniform(0, 5, N) for g in range(G)})
+            state.update({(abi.ARR_DNP_CUR, i): rng.uniform(0, 5, N) for i in range(D)})
+            state.update({(abi.ARR_DNP_LAST, i): rng.uniform(0, 5, N) for i in range(D)})
+        res = []
+        for lib in (oracle_lib, cuda_lib):
+            ctx = abi.Context(prob, lib)
+            for (w, i), v in state.items():
+                ctx.set_array(w, i, v)
+            r = {}
+            r["sres"] = ctx.scatter_residual(1)
+            ctx.update_scatter_source(1)
+            r["mgres"] = ctx.mg_residual()
+            r["k"] = ctx.update_k(0.9)
+            if mode == abi.MODE_EIGEN:
+                ctx.update_mg_source_eigen(2, 0.9)
+            else:
+                ctx.update_mg_source(2, 0.3)
+            if mode == abi.MODE_TRANSIENT:
+                ctx.step_dnps()
+                ctx.update_step_fluxes()
+            r["arrays"] = {k: ctx.get_array(*k) for k in state}
+            res.append(r)
+        o, c = res
+        for k in state:
+            if k[0] in (abi.ARR_DNP_CUR, abi.ARR_DNP_LAST):   # exp() may differ in the last ulp
+                np.testing.assert_allclose(c["arrays"][k], o["arrays"][k], rtol=4e-16, atol=0)
+            else:
+                assert np.array_equal(c["arrays"][k], o["arrays"][k]), k
+        assert abs(c["sres"] / o["sres"] - 1) < 1e-13 and abs(c["mgres"] / o["mgres"] - 1) < 1e-13
+        assert abs(c["k"][0] / o["k"][0] - 1) < 1e-13 and c["k"][1] == o["k"][1] == 0.9
+
+
+def test_angle_shards_sum_to_whole(cuda_lib):
+    """Size-independent property used for multi-GPU: sweeps over disjoint ordinate shards add up."""
+    params, prob = synthetic_case("/tmp/doma_syn_32.xml", 32, G=2, mode="A", sweeps=1)
+    q = np.random.default_rng(4).uniform(0, 1, prob.n_cells)
+    def one(p):
+        ctx = abi.Context(p, cuda_lib)
+        ctx.reset_state(0.0)
+        ctx.set_array(abi.ARR_Q, 0, q)
+        ctx.sweep(0)
+        return ctx.get_array(abi.ARR_PHI_CUR, 0)
+    whole = one(prob)
+    from doma_b200.sharding import shard_ordinates
+    parts = sum(one(prob.with_ordinates(shard_ordinates(prob, r, 4))) for r in range(4))
+    assert relmax(parts, whole) <= 1e-12
+
+
+def test_mirror_symmetry_full_size(cuda_lib):
+    """128^3 S16 symmetric problem: phi must be mirror-symmetric in x, y and z (octant pairs swap)."""
+    n = 128
+    params, prob = synthetic_case("/tmp/doma_syn_sym.xml", n, G=1, mode="A", sweeps=1)
+    prob.mat_of_cell[:] = 0
+    q = np.zeros((n, n, n))
+    q[n // 2 - 4:n // 2 + 4, n // 2 - 4:n // 2 + 4, n // 2 - 4:n // 2 + 4] = 1.0
+    ctx = abi.Context(prob, cuda_lib)
+    ctx.reset_state(0.0)
+    ctx.set_array(abi.ARR_Q, 0, q.reshape(-1))
+    ctx.sweep(0)
+    phi = ctx.get_array(abi.ARR_PHI_CUR, 0).reshape(n, n, n)
+    assert np.all(phi > 0)
+    for ax in range(3):
+        assert relmax(np.flip(phi, axis=ax), phi) <= 1e-11
+    assert ctx.last_sweep_ms() > 0
