@@ -1,0 +1,320 @@
+#!/usr/bin/env python
+"""bench.py - sweep throughput of the B200 path on the synthetic 256^3 x 8-group x S16 case.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--n 256] [--impl reference]
+
+One "step" = one Gauss-Seidel pass over all G groups of the synthetic case (Mode B):
+for every group: source build -> sweep -> (phi all-reduce when N > 1) -> scattering residual ->
+scattering-source update; then the multigroup residual.  That is N_cells * N_ordinates * G
+cell-angle-group updates per step.  With N > 1 (launched by torchrun, one rank per GPU) the sweep
+units (octant x 32-ordinate batch) are dealt across ranks, each rank sweeps its ordinates over the
+full mesh and phi_cur is summed with ncclAllReduce: a fixed problem, "scaling": "strong".
+
+Printed JSON (rank 0, one line): the contract keys, plus
+  roofline     - the sweep kernel against the HBM roofline: 48 algorithmic bytes per update
+                 (3 face-flux reads + 3 writes, as the reference moves them) / CUDA-event time
+  cpu_baseline - the UNMODIFIED reference (oracle/_ref/ref_harness, OpenMP) timed on this box's
+                 host cores on a bounded 64^3 sample of the same case
+  e2e          - the same step driven through doma_b200_sweep_from_host with HOST buffers
+                 (q: pinned host -> device, phi_cur: device -> host, every sweep)
+--impl reference times the reference itself (rank 0 only) on the bounded sample, same metric.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "sweep cell-angle-group updates/s"
+UNIT = "updates/s"
+BYTES_PER_UPDATE = 48.0   # 3 upwind face reads + 3 downwind face writes x 8 B
+FP64_OPS_PER_UPDATE = 118.0  # 13 divisions + 105 other FP64 operations as the reference writes them
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        self.thread.join(timeout=2)
+        sm = sorted(float(r[0]) for r in self.rows if len(r) >= 7 and r[0].replace(".", "").isdigit())
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in self.rows if len(r) >= 7 for n, v in zip(names, r[3:7]) if v.lower().startswith("active")})
+        mx = max([float(r[1]) for r in self.rows if len(r) >= 7 and r[1].replace(".", "").isdigit()] or [0.0])
+        pw = max([float(r[2]) for r in self.rows if len(r) >= 7 and r[2].replace(".", "").isdigit()] or [0.0])
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None, "power_w_max": pw or None,
+                "samples": len(sm), "reasons": reasons}
+
+
+def run_reference_sample(n, G, steps, warmup, threads, mode="B"):
+    """Times the unmodified reference on a bounded sample; returns (updates/s, seconds per step, description)."""
+    from doma_b200.synthetic import synthetic_xml
+
+    harness = os.path.join(ROOT, "oracle", "_ref", "ref_harness")
+    if not os.path.exists(harness):
+        return None, None, "oracle/_ref/ref_harness missing (build() compiles it where /root/reference exists)"
+    tmp = tempfile.mkdtemp(prefix="doma_ref_")
+    xml = os.path.join(tmp, "sample.xml")
+    with open(xml, "w") as f:
+        f.write(synthetic_xml(n, G=G, mode=mode, sweeps=1))
+    env = dict(os.environ, OMP_NUM_THREADS=str(threads), OMP_PROC_BIND="false")
+    times = []
+    for i in range(warmup + steps):
+        r = subprocess.run([harness, xml, str(threads), os.path.join(tmp, "out"), "--no-dump"], capture_output=True, text=True, env=env)
+        if r.returncode != 0:
+            return None, None, "ref_harness failed: " + r.stderr[-200:]
+        sec = float(r.stdout.rsplit("solve_seconds=", 1)[1].split()[0])
+        if i >= warmup:
+            times.append(sec)
+    upd = float(n) ** 3 * 512 * (G if mode == "B" else 1)
+    sec = sum(times) / len(times)
+    what = f"one sweep of each of the {G} groups (Mode B)" if mode == "B" else "one sweep of group 0 (Mode A)"
+    return upd / sec, sec, (f"unmodified reference (ref_harness), synthetic {n}^3 cells x 512 ordinates, {what}, "
+                            f"OpenMP {threads} threads, solve time only, mean of {steps} run(s) after {warmup} warm-up")
+
+
+def host_threads():
+    n = os.cpu_count() or 1
+    try:
+        n = len(os.sched_getaffinity(0))
+    except Exception:
+        pass
+    # the reference parallelises over the ordinates of ONE octant: 64 for S16, more threads cannot help
+    return max(1, min(n, 64))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--n", type=int, default=256, help="cells per axis of the synthetic cube")
+    ap.add_argument("--groups", type=int, default=8)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--tile", default="", help="TYxTZ override of the KBA tile, e.g. 4x8")
+    ap.add_argument("--ref-n", type=int, default=64, help="cells per axis of the bounded CPU sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    a = ap.parse_args()
+    a.warmup = max(a.warmup, 3) if a.impl == "b200" else max(a.warmup, 1)
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    G, n = a.groups, a.n
+    config = {"workload": f"synthetic 3D {n}^3 cells, {G} groups, S16 GC quadrature (np=na=8, 512 ordinates), TWDD, Mode B "
+                          f"(one sweep per group, Gauss-Seidel source build between)",
+              "cells": n ** 3, "ordinates": 512, "groups": G, "parallelism": f"angle-sharded x{world}" if world > 1 else "1 GPU",
+              "l2": "working set (face planes + flux arrays, > 1 GB) exceeds the 126 MB L2; no explicit flush"}
+
+    if a.impl == "reference":
+        if rank != 0:
+            return 0
+        T = host_threads()
+        v, sec, desc = run_reference_sample(a.ref_n, G, a.steps, a.warmup, T)
+        if v is None:
+            print(json.dumps({"impl": "reference", "unavailable": desc}))
+            return 0
+        print(json.dumps({
+            "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
+            "warmup": a.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic", "config": config,
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": T, "kind": "reference", "sample": desc},
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+        return 0
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    from doma_b200 import abi
+    from doma_b200.sharding import make_allreduce, shard_ordinates
+    from doma_b200.synthetic import synthetic_case
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: there is no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    xml = os.path.join(tempfile.gettempdir(), f"doma_bench_{n}_{G}_r{rank}.xml")
+    params, prob = synthetic_case(xml, n, G=G, mode="B")
+    prob.device = local
+    full_ord = prob.n_ord
+    if world > 1:
+        prob = prob.with_ordinates(shard_ordinates(prob, rank, world))
+    ctx = abi.Context(prob)
+    stream = torch.cuda.Stream(device=local)
+    ctx.set_stream(stream.cuda_stream)      # the context launches on this stream, so torch events see its kernels
+    if a.tile:
+        ty, tz = [int(v) for v in a.tile.lower().split("x")]
+        ctx.set_tile(8, ty, tz)
+    allreduce = make_allreduce(ctx) if world > 1 else None
+    N = prob.n_cells
+    updates_per_step = float(N) * full_ord * G
+
+    def step():
+        for g in range(G):
+            ctx.update_mg_source(g, 0.0)
+            ctx.sweep(g)
+            if allreduce is not None:
+                allreduce(ctx)
+            ctx.scatter_residual(g)
+            ctx.update_scatter_source(g)
+        return ctx.mg_residual()
+
+    def barrier():
+        ctx.synchronize()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+
+    ctx.reset_state(0.0)
+    for _ in range(a.warmup):
+        step()
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = ctx.info(abi.INFO_KERNEL_LAUNCHES)
+    sweep_ms = []
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
+    ev0.record(stream)
+    # device time: events on the context's stream bracket every sweep (last_sweep_ms); the whole
+    # region is bracketed by stream synchronisation + barrier, so wall == device time here
+    for _ in range(a.steps):
+        for g in range(G):
+            ctx.update_mg_source(g, 0.0)
+            ctx.sweep(g)
+            if allreduce is not None:
+                allreduce(ctx)
+            ctx.scatter_residual(g)      # synchronises the stream
+            sweep_ms.append(ctx.last_sweep_ms())
+            ctx.update_scatter_source(g)
+        ctx.mg_residual()
+    ev1.record(stream)
+    barrier()
+    wall = time.perf_counter() - t0
+    dt = ev0.elapsed_time(ev1) * 1e-3       # device time of the K steps (CUDA events on the launching stream)
+    launches = ctx.info(abi.INFO_KERNEL_LAUNCHES) - l0
+    clocks = sampler.stop() if rank == 0 else None
+    if world > 1:
+        t = torch.tensor([dt], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dt = float(t.item())
+        sm = torch.tensor([sum(sweep_ms) / len(sweep_ms)], dtype=torch.float64, device="cuda")
+        dist.all_reduce(sm, op=dist.ReduceOp.MAX)
+        mean_sweep_ms = float(sm.item())
+    else:
+        mean_sweep_ms = sum(sweep_ms) / len(sweep_ms)
+    value = updates_per_step * a.steps / dt
+
+    # ---- end to end through the host-buffer ABI call (q in pinned host memory, phi back to host) ----
+    e2e = None
+    if not a.no_e2e:
+        qh = torch.empty((G, N), dtype=torch.float64).pin_memory()
+        ph = torch.empty((N,), dtype=torch.float64).pin_memory()
+        qh.copy_(torch.rand((G, N), dtype=torch.float64, generator=torch.Generator().manual_seed(1)))
+        qn, pn = qh.numpy(), ph.numpy()
+
+        def e2e_step():
+            for g in range(G):
+                ctx.sweep_from_host(g, qn[g], pn)   # all-reduces phi_cur before the D2H when sharded
+            return float(pn[0])
+
+        for _ in range(2):
+            e2e_step()
+        barrier()
+        ev0.record(stream)
+        for _ in range(a.steps):
+            e2e_step()
+        ev1.record(stream)
+        barrier()
+        de = ev0.elapsed_time(ev1) * 1e-3
+        if world > 1:
+            t = torch.tensor([de], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            de = float(t.item())
+        e2e = {"value": updates_per_step * a.steps / de, "unit": UNIT, "h2d_bytes_per_step": 8 * N * G,
+               "d2h_bytes_per_step": 8 * N * G, "ms_per_step": de / a.steps * 1e3,
+               "api": "doma_b200_sweep_from_host (C ABI, host buffers) per group"}
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+
+    peak, peak_src = measured_peaks()
+    upd_per_launch = float(N) * prob.n_ord
+    achieved = upd_per_launch * BYTES_PER_UPDATE / (mean_sweep_ms * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": "sweep_kernel<3,TWDD>", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                "algorithmic_bytes_per_update": BYTES_PER_UPDATE, "updates_per_launch": upd_per_launch,
+                "launch_ms": mean_sweep_ms, "kernel_updates_per_s": upd_per_launch / (mean_sweep_ms * 1e-3),
+                "fp64_gflops_algorithmic": upd_per_launch * FP64_OPS_PER_UPDATE / (mean_sweep_ms * 1e-3) / 1e9,
+                "sweep_share_of_step": mean_sweep_ms * G * a.steps / (dt * 1e3)}
+    prof = os.path.join(ROOT, "profiles", "sweep_traffic.json")
+    if os.path.exists(prof):
+        try:
+            roofline["traffic"] = json.load(open(prof)).get("dram_bytes_per_launch")
+        except Exception:
+            pass
+    cpu = None
+    if not a.no_cpu_baseline and world == 1:
+        T = host_threads()
+        v, sec, desc = run_reference_sample(a.ref_n, G, 1, 1, T, mode="A")
+        if v is not None:
+            cpu = {"value": v, "unit": UNIT, "cores": T, "kind": "reference", "sample": desc}
+        else:
+            cpu = {"value": None, "unit": UNIT, "cores": T, "kind": "reference", "sample": desc}
+    out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+           "ms_per_step": dt / a.steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+           "data": "synthetic", "config": config, "grind_ns": 1e9 / value, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
+           "gpu_launches": int(launches), "clocks": clocks, "wall_ms_per_step": wall / a.steps * 1e3,
+           "tile": a.tile or "default"}
+    print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -407,7 +407,7 @@ doma_b200_sweep(doma_b200_ctx * c, int32_t g)
 }
 
 // Host-buffer form of sweep(g) for end-to-end timing: q (N doubles, host) -> device, phi_cur = 0,
-// sweep, phi_cur -> host.  Synchronous.
+// sweep, (all-reduce over ranks when a communicator exists,) phi_cur -> host.  Synchronous.
 int
 doma_b200_sweep_from_host(doma_b200_ctx * c, int32_t g, const double * q_host, double * phi_cur_out)
 {
@@ -415,8 +415,10 @@ doma_b200_sweep_from_host(doma_b200_ctx * c, int32_t g, const double * q_host, d
   CHECK_GROUP(c, g);
   DOMA_CUDA(c, cudaMemcpyAsync(c->q, q_host, sizeof(double) * c->N, cudaMemcpyHostToDevice, c->stream));
   DOMA_CUDA(c, cudaMemsetAsync(c->phi_cur, 0, sizeof(double) * c->N, c->stream));
-  const int rc = doma_launch_sweep(c, g);
+  int rc = doma_launch_sweep(c, g);
   if (rc)
+    return rc;
+  if (c->nccl_comm && (rc = doma_b200_allreduce_phi_cur(c)))
     return rc;
   DOMA_CUDA(c, cudaMemcpyAsync(phi_cur_out, c->phi_cur, sizeof(double) * c->N, cudaMemcpyDeviceToHost, c->stream));
   DOMA_CUDA(c, cudaStreamSynchronize(c->stream));

@@ -1,0 +1,16 @@
+#!/bin/bash
+# Run on the B200 box (gpurun): GPU tests, the bench, an ncu launch list and one full capture of the sweep kernel.
+mkdir -p gpurun_out
+nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,memory.total --format=csv
+nproc; free -g | head -2
+timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -5
+python bench.py ${BENCH_ARGS:-} > gpurun_out/bench.json 2> gpurun_out/bench.err; tail -c 3000 gpurun_out/bench.json; tail -5 gpurun_out/bench.err
+python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/bench_ref.json 2>> gpurun_out/bench.err; cat gpurun_out/bench_ref.json
+if [ -n "$DO_NCU" ]; then
+  P="python bench.py --n 128 --steps 1 --warmup 3 --no-cpu-baseline --no-e2e"
+  $P > gpurun_out/plain.log 2>&1 &&
+  ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv $P > gpurun_out/ncu_list.log 2>&1
+  $P > gpurun_out/plain2.log 2>&1 &&
+  ncu --set full --clock-control none --import-source on -k regex:sweep_kernel -s 26 -c 1 -o gpurun_out/prof_sweep -f $P > gpurun_out/ncu_full.log 2>&1
+  tail -3 gpurun_out/ncu_full.log
+fi
