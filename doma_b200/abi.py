@@ -4,9 +4,8 @@ The product binds exactly one library, ``doma_b200/libdoma_b200.so`` (hand-writt
 built by ``__graft_entry__.build()``), through :func:`load_library`.  There is NO CPU fallback:
 if that library is missing, or no CUDA device is usable, loading / context creation raises.
 
-The binding itself is generic in (path, symbol prefix) so that the test-suite can drive the CPU
-oracle (``oracle/libdoma_oracle.so``, prefix ``doma_oracle_``) through the very same host code;
-nothing in this package ever passes an oracle path.
+The binding itself is generic in (path, symbol prefix) so that the test-suite can drive its CPU
+checker through the very same host code; nothing in this package ever passes another path.
 """
 from __future__ import annotations
 
