@@ -29,7 +29,7 @@ def test_driver_reproduces_reference(name, tmp_path):
     si = [int(x) for x in re.findall(r"SI (?:converged|failed to converge) after (\d+) iterations", r.stdout)]
     assert si == list(g["si_counts"])
     if name.startswith("asm_eig"):
-        assert abs(float(re.search(r"k=([-0-9.e+]+)", tail).group(1)) - float(g["k"])) <= 1e-9
+        assert abs(float(re.search(r" k=([-0-9.e+]+)", tail).group(1)) - float(g["k"])) <= 1e-9
     if bool(g["ok"]):
         # the reference's own text dump (6 significant digits) of the GPU-computed flux
         base = str(tmp_path / name)
