@@ -129,6 +129,7 @@ def main():
     ap.add_argument("--groups", type=int, default=8)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--tile", default="", help="TYxTZ override of the KBA tile, e.g. 4x8")
+    ap.add_argument("--variant", type=int, default=0, help="ordinates per lane of the sweep (1 or 2); 0 = library default")
     ap.add_argument("--ref-n", type=int, default=64, help="cells per axis of the bounded CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -186,6 +187,8 @@ def main():
     if a.tile:
         ty, tz = [int(v) for v in a.tile.lower().split("x")]
         ctx.set_tile(8, ty, tz)
+    if a.variant:
+        ctx.set_sweep_variant(a.variant)
     allreduce = make_allreduce(ctx) if world > 1 else None
     N = prob.n_cells
     updates_per_step = float(N) * full_ord * G
@@ -256,9 +259,14 @@ def main():
         qn, pn = qh.numpy(), ph.numpy()
 
         def e2e_step():
+            # the same Gauss-Seidel pass as step(), with the sweep driven through the host-buffer call:
+            # q goes pinned host -> device, phi_cur comes back device -> host, every sweep
             for g in range(G):
+                ctx.update_mg_source(g, 0.0)
                 ctx.sweep_from_host(g, qn[g], pn)   # all-reduces phi_cur before the D2H when sharded
-            return float(pn[0])
+                ctx.scatter_residual(g)
+                ctx.update_scatter_source(g)
+            return ctx.mg_residual() + float(pn[0])
 
         for _ in range(2):
             e2e_step()
@@ -275,7 +283,7 @@ def main():
             de = float(t.item())
         e2e = {"value": updates_per_step * a.steps / de, "unit": UNIT, "h2d_bytes_per_step": 8 * N * G,
                "d2h_bytes_per_step": 8 * N * G, "ms_per_step": de / a.steps * 1e3,
-               "api": "doma_b200_sweep_from_host (C ABI, host buffers) per group"}
+               "api": "doma_b200_sweep_from_host (C ABI, host buffers) per group + the step's source/residual calls"}
 
     if rank != 0:
         if world > 1:
@@ -309,7 +317,8 @@ def main():
            "ms_per_step": dt / a.steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
            "data": "synthetic", "config": config, "grind_ns": 1e9 / value, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
            "gpu_launches": int(launches), "clocks": clocks, "wall_ms_per_step": wall / a.steps * 1e3,
-           "tile": a.tile or "default"}
+           "tile": a.tile or "default", "sweep_variant": int(ctx.info(abi.INFO_SWEEP_VARIANT)),
+           "units_per_rank": int(ctx.info(abi.INFO_N_UNITS))}
     print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()

@@ -26,7 +26,7 @@ SCHEME_DD, SCHEME_TWDD = 0, 1
 STEP_NONE, STEP_INSERT, STEP_REMOVE, STEP_BOTH = -1, 0, 1, 2
 MAT_HAS_SRC, MAT_HAS_CHI_P, MAT_HAS_NU_SIGMA_F = 1, 2, 4
 ARR_PHI_TOT, ARR_PHI_PREV, ARR_PHI_LAST, ARR_DNP_CUR, ARR_DNP_LAST, ARR_Q, ARR_PHI_CUR = range(7)
-INFO_KERNEL_LAUNCHES, INFO_SWEEP_VARIANT, INFO_N_CELLS, INFO_N_ORD, INFO_FACE_BYTES, INFO_DEVICE_BYTES = range(6)
+INFO_KERNEL_LAUNCHES, INFO_SWEEP_VARIANT, INFO_N_CELLS, INFO_N_ORD, INFO_FACE_BYTES, INFO_DEVICE_BYTES, INFO_N_UNITS, INFO_N_TILES = range(8)
 
 _pd = C.POINTER(C.c_double)
 _pi = C.POINTER(C.c_int32)

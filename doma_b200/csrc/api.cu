@@ -39,74 +39,106 @@ alloc_zero(doma_b200_ctx * c, double ** dst, size_t n)
   return 0;
 }
 
-// Regroup this context's ordinates into sweep units: per octant, ceil(count/32) batches of
-// near-equal size; lanes beyond a batch are padded with a harmless direction and weight 0.
-int
-build_units(doma_b200_ctx * c, const doma_b200_problem * p)
+template <typename T>
+void
+free_dev(T *& p)
 {
+  if (p)
+    cudaFree(p);
+  p = nullptr;
+}
+} // namespace
+
+// Regroup this context's ordinates into sweep units: per octant, ceil(count/(32 V)) units of
+// near-equal size, each split over V batches of <= 32 lanes; lanes beyond a batch are padded with a
+// harmless direction and weight 0.  Also (re)allocates the face planes and the tile table.
+int
+doma_build_units(doma_b200_ctx * c, int V)
+{
+  if (V != 1 && !(V == 2 && c->dims == 3))
+  {
+    snprintf(c->err, DOMA_MAX_ERR, "sweep variant: %d ordinates per lane not supported for a %dD problem", V, c->dims);
+    return 4;
+  }
+  DOMA_CUDA(c, cudaStreamSynchronize(c->stream));
+  const int L = DOMA_LANES * V;
   std::vector<int> uo;
   std::vector<double> mu, eta, xi, w;
   std::vector<SweepUnit> units;
   for (int oct = 0; oct < 8; ++oct)
   {
     std::vector<int> idx;
-    for (int n = 0; n < p->n_ord; ++n)
-      if (p->ord_octant[n] == oct)
+    for (int n = 0; n < c->n_ord; ++n)
+      if (c->h_ord_octant[n] == oct)
         idx.push_back(n);
     if (idx.empty())
       continue;
-    if (c->dims == 2 && (oct & 1))
-    {
-      snprintf(c->err, DOMA_MAX_ERR, "create: 2D problems sweep only the xi>0 octants (PPP, PMP, MPP, MMP); got octant %d", oct);
-      return 9;
-    }
     const int cnt = (int)idx.size();
-    const int nb = (cnt + DOMA_LANES - 1) / DOMA_LANES;
+    const int nb = (cnt + L - 1) / L;
     int pos = 0;
     for (int b = 0; b < nb; ++b)
     {
       const int sz = cnt / nb + (b < cnt % nb ? 1 : 0);
       units.push_back(SweepUnit{oct, sz});
       uo.push_back(oct);
-      for (int l = 0; l < DOMA_LANES; ++l)
+      for (int v = 0; v < V; ++v)
       {
-        if (l < sz)
+        const int vsz = sz / V + (v < sz % V ? 1 : 0);
+        for (int l = 0; l < DOMA_LANES; ++l)
         {
-          const int n = idx[pos + l];
-          // parallelSweepOctant takes std::abs of each component (src/TransportSolver3D.cpp:645-649)
-          mu.push_back(fabs(p->mu[n]));
-          eta.push_back(fabs(p->eta[n]));
-          xi.push_back(fabs(p->xi[n]));
-          w.push_back(p->w[n]);
+          if (l < vsz)
+          {
+            const int n = idx[pos + l];
+            // parallelSweepOctant takes std::abs of each component (src/TransportSolver3D.cpp:645-649)
+            mu.push_back(fabs(c->h_mu[n]));
+            eta.push_back(fabs(c->h_eta[n]));
+            xi.push_back(fabs(c->h_xi[n]));
+            w.push_back(c->h_w[n]);
+          }
+          else
+          {
+            mu.push_back(1.0);
+            eta.push_back(1.0);
+            xi.push_back(1.0);
+            w.push_back(0.0);
+          }
         }
-        else
-        {
-          mu.push_back(1.0);
-          eta.push_back(1.0);
-          xi.push_back(1.0);
-          w.push_back(0.0);
-        }
+        pos += vsz;
       }
-      pos += sz;
     }
   }
+  c->device_bytes -= c->face_bytes;
+  free_dev(c->unit_octant), free_dev(c->u_mu), free_dev(c->u_eta), free_dev(c->u_xi), free_dev(c->u_w);
+  free_dev(c->face_x), free_dev(c->face_y), free_dev(c->face_z);
+  free(c->h_units);
+  c->V = V;
   c->n_units = (int)units.size();
   c->h_units = (SweepUnit *)malloc(sizeof(SweepUnit) * (units.size() + 1));
   memcpy(c->h_units, units.data(), sizeof(SweepUnit) * units.size());
   int rc = 0;
-  if ((rc = upload(c, &c->unit_octant, uo.data(), uo.size())))
+  if ((rc = upload(c, &c->unit_octant, uo.data(), uo.size())) || (rc = upload(c, &c->u_mu, mu.data(), mu.size())) ||
+      (rc = upload(c, &c->u_eta, eta.data(), eta.size())) || (rc = upload(c, &c->u_xi, xi.data(), xi.size())) ||
+      (rc = upload(c, &c->u_w, w.data(), w.size())))
     return rc;
-  if ((rc = upload(c, &c->u_mu, mu.data(), mu.size())))
-    return rc;
-  if ((rc = upload(c, &c->u_eta, eta.data(), eta.size())))
-    return rc;
-  if ((rc = upload(c, &c->u_xi, xi.data(), xi.size())))
-    return rc;
-  if ((rc = upload(c, &c->u_w, w.data(), w.size())))
-    return rc;
-  return 0;
+  // face planes per unit, angle fastest
+  const size_t U = c->n_units;
+  c->face_bytes = 0;
+  if (U)
+  {
+    const size_t nfx = U * c->nz * c->ny * L, nfy = U * c->nz * c->nx * L, nfz = c->dims == 3 ? U * c->ny * c->nx * L : 0;
+    DOMA_CUDA(c, cudaMalloc(&c->face_x, sizeof(double) * nfx));
+    DOMA_CUDA(c, cudaMalloc(&c->face_y, sizeof(double) * nfy));
+    if (nfz)
+      DOMA_CUDA(c, cudaMalloc(&c->face_z, sizeof(double) * nfz));
+    c->face_bytes = sizeof(double) * (nfx + nfy + nfz);
+    c->device_bytes += c->face_bytes;
+  }
+  // default tile: 8 x 4 x 8 in 3D, 8 x 4 in 2D
+  return doma_sweep_setup_tiles(c, c->tile_y > 0 ? c->tile_y : 4, c->dims == 3 ? (c->tile_z > 0 ? c->tile_z : 8) : 1);
 }
 
+namespace
+{
 int
 create_impl(doma_b200_ctx * c, const doma_b200_problem * p)
 {
@@ -186,8 +218,9 @@ create_impl(doma_b200_ctx * c, const doma_b200_problem * p)
   UP(step_t_remove, p->step_t_remove, M);
   UP(step_src, p->step_src, M * G);
 #undef UP
-  if ((rc = alloc_zero(c, &c->sig_eff, M)))
+  if ((rc = alloc_zero(c, &c->sig_cell, (size_t)c->N)))
     return rc;
+  c->sig_cell_group = -1;
   const size_t N = (size_t)c->N;
   if ((rc = alloc_zero(c, &c->phi_tot, G * N)) || (rc = alloc_zero(c, &c->phi_prev, G * N)) || (rc = alloc_zero(c, &c->q, N)) ||
       (rc = alloc_zero(c, &c->phi_cur, N)))
@@ -199,30 +232,39 @@ create_impl(doma_b200_ctx * c, const doma_b200_problem * p)
     if (D && ((rc = alloc_zero(c, &c->dnp_cur, D * N)) || (rc = alloc_zero(c, &c->dnp_last, D * N))))
       return rc;
   }
-  if ((rc = build_units(c, p)))
-    return rc;
-  // face planes per unit, angle fastest
-  const size_t U = c->n_units;
-  c->face_bytes = 0;
-  if (U)
+  // host copy of the ordinates (the sweep variant can be changed after create)
   {
-    const size_t nfx = U * c->nz * c->ny * 32, nfy = U * c->nz * c->nx * 32, nfz = c->dims == 3 ? U * c->ny * c->nx * 32 : 0;
-    DOMA_CUDA(c, cudaMalloc(&c->face_x, sizeof(double) * nfx));
-    DOMA_CUDA(c, cudaMalloc(&c->face_y, sizeof(double) * nfy));
-    if (nfz)
-      DOMA_CUDA(c, cudaMalloc(&c->face_z, sizeof(double) * nfz));
-    c->face_bytes = sizeof(double) * (nfx + nfy + nfz);
-    c->device_bytes += c->face_bytes;
+    const size_t n = (size_t)(c->n_ord > 0 ? c->n_ord : 1);
+    c->h_ord_octant = (int32_t *)calloc(n, sizeof(int32_t));
+    c->h_mu = (double *)calloc(n, sizeof(double)), c->h_eta = (double *)calloc(n, sizeof(double));
+    c->h_xi = (double *)calloc(n, sizeof(double)), c->h_w = (double *)calloc(n, sizeof(double));
+    int per_oct[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (int i = 0; i < c->n_ord; ++i)
+    {
+      const int o = p->ord_octant[i];
+      if (o < 0 || o > 7 || (c->dims == 2 && (o & 1)))
+      {
+        snprintf(c->err, DOMA_MAX_ERR, "create: ordinate %d has octant %d%s", i, o,
+                 c->dims == 2 ? "; 2D problems sweep only the xi>0 octants (PPP, PMP, MPP, MMP)" : "");
+        return 9;
+      }
+      c->h_ord_octant[i] = o, c->h_mu[i] = p->mu[i], c->h_eta[i] = p->eta[i], c->h_xi[i] = p->xi[i], c->h_w[i] = p->w[i];
+      per_oct[o] += 1;
+    }
+    int most = 0;
+    for (int o = 0; o < 8; ++o)
+      most = per_oct[o] > most ? per_oct[o] : most;
+    // two ordinates per lane as soon as an octant does not fit one warp (3D)
+    int V = (c->dims == 3 && most > DOMA_LANES) ? 2 : 1;
+    if (const char * e = getenv("DOMA_B200_V"))
+      V = (atoi(e) == 2 && c->dims == 3) ? 2 : 1;
+    DOMA_CUDA(c, cudaMalloc(&c->work_counter, sizeof(int)));
+    if ((rc = doma_build_units(c, V)))
+      return rc;
   }
-  DOMA_CUDA(c, cudaMalloc(&c->work_counter, sizeof(int)));
   DOMA_CUDA(c, cudaMalloc(&c->red_partial, sizeof(double) * 2 * 1184));
   DOMA_CUDA(c, cudaMalloc(&c->red_out, sizeof(double) * 2));
   DOMA_CUDA(c, cudaMallocHost(&c->h_red, sizeof(double) * 2));
-  c->sweep_variant = 1;
-  // default tile: 8 x 4 x 8 in 3D (8 KB of shared memory per warp), 8 x 4 in 2D
-  int tz = c->dims == 3 ? 8 : 1;
-  if ((rc = doma_sweep_setup_tiles(c, 4, tz)))
-    return rc;
   return 0;
 }
 
@@ -307,7 +349,7 @@ doma_b200_destroy(doma_b200_ctx * c)
     g_nccl.CommDestroy(c->nccl_comm);
   void * ptrs[] = {c->dx, c->dy, c->dz, c->rdx, c->rdy, c->rdz, c->mat, c->mat_flags, c->n_delayed, c->step_type, c->sigma_t,
                    c->sigma_s, c->nu_sigma_f, c->chi_p, c->src, c->inv_v, c->chi_d, c->beta, c->lambda, c->step_t_insert,
-                   c->step_t_remove, c->step_src, c->sig_eff, c->phi_tot, c->phi_prev, c->phi_last, c->dnp_cur, c->dnp_last,
+                   c->step_t_remove, c->step_src, c->sig_cell, c->phi_tot, c->phi_prev, c->phi_last, c->dnp_cur, c->dnp_last,
                    c->q, c->phi_cur, c->unit_octant, c->u_mu, c->u_eta, c->u_xi, c->u_w, c->tile_order, c->face_x, c->face_y,
                    c->face_z, c->tile_done, c->work_counter, c->red_partial, c->red_out};
   for (void * p : ptrs)
@@ -322,6 +364,7 @@ doma_b200_destroy(doma_b200_ctx * c)
   if (c->own_stream && c->stream)
     cudaStreamDestroy(c->stream);
   free(c->h_units);
+  free(c->h_ord_octant), free(c->h_mu), free(c->h_eta), free(c->h_xi), free(c->h_w);
   free(c);
   return 0;
 }
@@ -532,7 +575,7 @@ doma_b200_get_info(doma_b200_ctx * c, int32_t what, int64_t * out)
   switch (what)
   {
     case DOMA_INFO_KERNEL_LAUNCHES: *out = c->launches; break;
-    case DOMA_INFO_SWEEP_VARIANT: *out = c->sweep_variant; break;
+    case DOMA_INFO_SWEEP_VARIANT: *out = c->V; break;
     case DOMA_INFO_N_CELLS: *out = c->N; break;
     case DOMA_INFO_N_ORD: *out = c->n_ord; break;
     case DOMA_INFO_FACE_BYTES: *out = c->face_bytes; break;
@@ -547,15 +590,15 @@ doma_b200_get_info(doma_b200_ctx * c, int32_t what, int64_t * out)
 int
 doma_b200_set_sweep_variant(doma_b200_ctx * c, int32_t variant)
 {
-  if (!c)
-    return 1;
-  if (variant != 1)
+  ENTER(c);
+  if (variant != 1 && variant != 2)
   {
-    snprintf(c->err, DOMA_MAX_ERR, "set_sweep_variant: only variant 1 (persistent KBA tiles) exists");
+    snprintf(c->err, DOMA_MAX_ERR, "set_sweep_variant: variants are 1 and 2 (ordinates per lane)");
     return 4;
   }
-  c->sweep_variant = variant;
-  return 0;
+  if (variant == c->V)
+    return 0;
+  return doma_build_units(c, variant);
 }
 
 int

@@ -23,7 +23,7 @@
 struct SweepUnit
 {
   int octant;  // DOMA_OCT_*
-  int n_lanes; // active lanes (ordinates) in this unit, <= 32
+  int n_lanes; // ordinates in this unit, <= 32 V
 };
 
 struct doma_b200_ctx
@@ -42,26 +42,30 @@ struct doma_b200_ctx
   int32_t *mat_flags, *n_delayed, *step_type;
   double *sigma_t, *sigma_s, *nu_sigma_f, *chi_p, *src, *inv_v, *chi_d, *beta, *lambda;
   double *step_t_insert, *step_t_remove, *step_src;
-  double * sig_eff; // [M] total cross section the cell solve uses for the group being swept
+  double * sig_cell;  // [N] total cross section the cell solve uses, expanded per cell for the group being swept
+  int sig_cell_group; // group sig_cell currently holds, -1 = none
 
   // state
   double *phi_tot, *phi_prev, *phi_last, *dnp_cur, *dnp_last, *q, *phi_cur;
 
-  // quadrature, regrouped into sweep units (octant x batch of <=32 ordinates), lane-major
+  // quadrature: host copy of this context's ordinates as given at create, and the same regrouped
+  // into sweep units (octant x V batches of <=32 ordinates), lane-major
+  int32_t * h_ord_octant;
+  double *h_mu, *h_eta, *h_xi, *h_w; // [n_ord] signed, as passed in
+  int V;               // ordinates per lane: 1, or 2 when octants hold more than 32 ordinates (3D)
   int n_units;
   SweepUnit * h_units; // host copy
   int * unit_octant;   // [U]
-  double *u_mu, *u_eta, *u_xi, *u_w; // [U][32] absolute direction cosines; padding lanes: 1,1,1,w=0
+  double *u_mu, *u_eta, *u_xi, *u_w; // [U][V][32] absolute direction cosines; padding lanes: 1,1,1,w=0
 
   // sweep scratch
   int tile_x, tile_y, tile_z; // tile_x is fixed to 8 by the kernel (row held in registers)
   int ntx, nty, ntz, n_tiles;
   uint32_t * tile_order; // [n_tiles] packed (I',J',K') sorted by I'+J'+K'
-  double *face_x, *face_y, *face_z; // [U][nz][ny][32], [U][nz][nx][32], [U][ny][nx][32]
+  double *face_x, *face_y, *face_z; // [U][nz][ny][32V], [U][nz][nx][32V], [U][ny][nx][32V]
   int * tile_done;                   // [U][n_tiles] epoch of completion
   int * work_counter;                // [1]
   int epoch;
-  int sweep_variant;
   int64_t face_bytes, device_bytes;
 
   // reductions
@@ -104,6 +108,9 @@ int doma_launch_scatter_residual(doma_b200_ctx * c, int g); // leaves (diff, tot
 int doma_launch_mg_residual(doma_b200_ctx * c);
 int doma_launch_k_sums(doma_b200_ctx * c, double k);
 int doma_launch_sig_eff(doma_b200_ctx * c, int g);
+
+// api.cu: (re)build sweep units, face planes and the tile table for V ordinates per lane
+int doma_build_units(doma_b200_ctx * c, int V);
 
 // sweep.cu
 int doma_sweep_setup_tiles(doma_b200_ctx * c, int ty, int tz);

@@ -179,19 +179,21 @@ scatter_source_kernel(int64_t N, int G, int g, double f, const int32_t * __restr
   phi_cur[i] = 0.0;
 }
 
-// total cross section seen by the cell solve for group g: sigma_t, plus inv_v/dt for 2D transients
-// (the 3D sweeps never pass mode/dt to the cell solve)
+// total cross section seen by the cell solve for group g, expanded per cell so the sweep reads it
+// without the material indirection: sigma_t, plus inv_v/dt for 2D transients (the 3D sweeps never
+// pass mode/dt to the cell solve).  12 B per cell per sweep against the sweep's hundreds.
 __global__ void
-sig_eff_kernel(int M, int G, int g, int add_inv_v, double dt, const double * __restrict__ sigma_t,
-               const double * __restrict__ inv_v, double * __restrict__ sig_eff)
+sig_cell_kernel(int64_t N, int G, int g, int add_inv_v, double dt, const int32_t * __restrict__ mat,
+                const double * __restrict__ sigma_t, const double * __restrict__ inv_v, double * __restrict__ sig_cell)
 {
-  const int m = blockIdx.x * blockDim.x + threadIdx.x;
-  if (m >= M)
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= N)
     return;
+  const int m = mat[i];
   double tot = sigma_t[m * G + g];
   if (add_inv_v)
     tot += inv_v[m * G + g] / dt;
-  sig_eff[m] = tot;
+  sig_cell[i] = tot;
 }
 
 // ---- reductions: block partials in a fixed grid, then one block sums the partials in order ----
@@ -432,8 +434,12 @@ int
 doma_launch_sig_eff(doma_b200_ctx * c, int g)
 {
   const int add = (c->dims == 2 && c->mode == DOMA_MODE_TRANSIENT) ? 1 : 0;
-  sig_eff_kernel<<<(c->M + 63) / 64, 64, 0, c->stream>>>(c->M, c->G, g, add, c->dt, c->sigma_t, c->inv_v, c->sig_eff);
+  if (c->sig_cell_group == g)
+    return 0; // already expanded for this group (repeated source iterations of one group)
+  sig_cell_kernel<<<ew_blocks(c->N), EW_THREADS, 0, c->stream>>>(c->N, c->G, g, add, c->dt, c->mat, c->sigma_t, c->inv_v,
+                                                                 c->sig_cell);
   c->launches += 1;
   DOMA_CUDA(c, cudaGetLastError());
+  c->sig_cell_group = g;
   return 0;
 }
