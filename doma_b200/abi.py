@@ -17,7 +17,7 @@ from typing import Dict, Optional
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libdoma_b200.so")
+LIB_PATH = os.environ.get("DOMA_B200_LIB") or os.path.join(_HERE, "libdoma_b200.so")  # the override is for kernel experiments only
 
 # enums of include/doma_b200.h (values are the reference's, include/TransportBase.h:20-62)
 OCT_PPP, OCT_PPM, OCT_PMP, OCT_PMM, OCT_MPP, OCT_MPM, OCT_MMP, OCT_MMM = range(8)
