@@ -55,9 +55,9 @@ free_dev(T *& p)
 int
 doma_build_units(doma_b200_ctx * c, int V)
 {
-  if (V != 1 && !(V == 2 && c->dims == 3))
+  if (V != 1)
   {
-    snprintf(c->err, DOMA_MAX_ERR, "sweep variant: %d ordinates per lane not supported for a %dD problem", V, c->dims);
+    snprintf(c->err, DOMA_MAX_ERR, "sweep variant: %d ordinates per lane not supported (only 1)", V);
     return 4;
   }
   DOMA_CUDA(c, cudaStreamSynchronize(c->stream));
@@ -251,15 +251,9 @@ create_impl(doma_b200_ctx * c, const doma_b200_problem * p)
       c->h_ord_octant[i] = o, c->h_mu[i] = p->mu[i], c->h_eta[i] = p->eta[i], c->h_xi[i] = p->xi[i], c->h_w[i] = p->w[i];
       per_oct[o] += 1;
     }
-    int most = 0;
-    for (int o = 0; o < 8; ++o)
-      most = per_oct[o] > most ? per_oct[o] : most;
-    // two ordinates per lane as soon as an octant does not fit one warp (3D)
-    int V = (c->dims == 3 && most > DOMA_LANES) ? 2 : 1;
-    if (const char * e = getenv("DOMA_B200_V"))
-      V = (atoi(e) == 2 && c->dims == 3) ? 2 : 1;
+    (void)per_oct;
     DOMA_CUDA(c, cudaMalloc(&c->work_counter, sizeof(int)));
-    if ((rc = doma_build_units(c, V)))
+    if ((rc = doma_build_units(c, 1)))
       return rc;
   }
   DOMA_CUDA(c, cudaMalloc(&c->red_partial, sizeof(double) * 2 * 1184));
@@ -591,9 +585,9 @@ int
 doma_b200_set_sweep_variant(doma_b200_ctx * c, int32_t variant)
 {
   ENTER(c);
-  if (variant != 1 && variant != 2)
+  if (variant != 1)
   {
-    snprintf(c->err, DOMA_MAX_ERR, "set_sweep_variant: variants are 1 and 2 (ordinates per lane)");
+    snprintf(c->err, DOMA_MAX_ERR, "set_sweep_variant: only variant 1 (persistent KBA tiles, one ordinate per lane) exists");
     return 4;
   }
   if (variant == c->V)

@@ -158,20 +158,18 @@ int doma_b200_device_ptr(doma_b200_ctx * ctx, int32_t which, int32_t index, void
 enum
 {
   DOMA_INFO_KERNEL_LAUNCHES = 0, /* kernels launched by this context so far */
-  DOMA_INFO_SWEEP_VARIANT = 1,   /* ordinates per lane of the persistent KBA sweep: 1 or 2 */
+  DOMA_INFO_SWEEP_VARIANT = 1,   /* 1 = persistent KBA tiles, one ordinate per lane (the only variant so far) */
   DOMA_INFO_N_CELLS = 2,
   DOMA_INFO_N_ORD = 3,
   DOMA_INFO_FACE_BYTES = 4,
   DOMA_INFO_DEVICE_BYTES = 5,
-  DOMA_INFO_N_UNITS = 6,         /* sweep units = (octant, batch of <= 32 x variant ordinates) */
+  DOMA_INFO_N_UNITS = 6,         /* sweep units = (octant, batch of <= 32 ordinates) */
   DOMA_INFO_N_TILES = 7          /* tiles of the KBA decomposition */
 };
 int doma_b200_get_info(doma_b200_ctx * ctx, int32_t what, int64_t * out);
-/* ordinates carried per warp lane (see DOMA_INFO_SWEEP_VARIANT): 1, or 2 (3D only; two independent
- * dependency chains per thread). Default: 2 when an octant holds more than 32 ordinates, else 1.
- * Rebuilds the sweep units, face planes and tile table. */
+/* select the sweep implementation (see DOMA_INFO_SWEEP_VARIANT); default 1 */
 int doma_b200_set_sweep_variant(doma_b200_ctx * ctx, int32_t variant);
-/* KBA tile extents in cells; tx must be 8 (the row a warp keeps in registers), ty <= 8. Rebuilds the tile table. */
+/* KBA tile extents in cells; tx must be 8 (the row a warp keeps in registers), ty <= 4. Rebuilds the tile table. */
 int doma_b200_set_tile(doma_b200_ctx * ctx, int32_t tx, int32_t ty, int32_t tz);
 /* device time in ms of the most recent doma_b200_sweep (CUDA events on the context's stream; synchronises) */
 int doma_b200_last_sweep_ms(doma_b200_ctx * ctx, float * out);
