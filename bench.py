@@ -130,6 +130,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--tile", default="", help="TYxTZ override of the KBA tile, e.g. 4x8")
     ap.add_argument("--ref-n", type=int, default=64, help="cells per axis of the bounded CPU sample")
+    ap.add_argument("--variant", type=int, default=0, help="sweep variant override (1 = row at a time, 2 = row pairs)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     a = ap.parse_args()
@@ -186,6 +187,8 @@ def main():
     if a.tile:
         ty, tz = [int(v) for v in a.tile.lower().split("x")]
         ctx.set_tile(8, ty, tz)
+    if a.variant:
+        ctx.set_sweep_variant(a.variant)
     allreduce = make_allreduce(ctx) if world > 1 else None
     N = prob.n_cells
     updates_per_step = float(N) * full_ord * G

@@ -9,6 +9,10 @@
 
 #include <vector>
 
+#ifndef DOMA_DEFAULT_VARIANT
+#define DOMA_DEFAULT_VARIANT 1
+#endif
+
 namespace
 {
 char g_create_err[DOMA_MAX_ERR] = "";
@@ -253,6 +257,10 @@ create_impl(doma_b200_ctx * c, const doma_b200_problem * p)
     }
     (void)per_oct;
     DOMA_CUDA(c, cudaMalloc(&c->work_counter, sizeof(int)));
+    c->sweep_variant = DOMA_DEFAULT_VARIANT;
+    if (const char * v = getenv("DOMA_B200_SWEEP_VARIANT"))
+      if (atoi(v) == 1 || atoi(v) == 2)
+        c->sweep_variant = atoi(v);
     if ((rc = doma_build_units(c, 1)))
       return rc;
   }
@@ -569,7 +577,7 @@ doma_b200_get_info(doma_b200_ctx * c, int32_t what, int64_t * out)
   switch (what)
   {
     case DOMA_INFO_KERNEL_LAUNCHES: *out = c->launches; break;
-    case DOMA_INFO_SWEEP_VARIANT: *out = c->V; break;
+    case DOMA_INFO_SWEEP_VARIANT: *out = c->sweep_variant; break;
     case DOMA_INFO_N_CELLS: *out = c->N; break;
     case DOMA_INFO_N_ORD: *out = c->n_ord; break;
     case DOMA_INFO_FACE_BYTES: *out = c->face_bytes; break;
@@ -585,14 +593,14 @@ int
 doma_b200_set_sweep_variant(doma_b200_ctx * c, int32_t variant)
 {
   ENTER(c);
-  if (variant != 1)
+  if (variant != 1 && variant != 2)
   {
-    snprintf(c->err, DOMA_MAX_ERR, "set_sweep_variant: only variant 1 (persistent KBA tiles, one ordinate per lane) exists");
+    snprintf(c->err, DOMA_MAX_ERR, "set_sweep_variant: variants are 1 (one row at a time) and 2 (row pairs), got %d", variant);
     return 4;
   }
-  if (variant == c->V)
-    return 0;
-  return doma_build_units(c, variant);
+  DOMA_CUDA(c, cudaStreamSynchronize(c->stream));
+  c->sweep_variant = variant;
+  return 0;
 }
 
 int

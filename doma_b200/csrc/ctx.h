@@ -52,7 +52,8 @@ struct doma_b200_ctx
   // into sweep units (octant x V batches of <=32 ordinates), lane-major
   int32_t * h_ord_octant;
   double *h_mu, *h_eta, *h_xi, *h_w; // [n_ord] signed, as passed in
-  int V;               // ordinates per lane: 1, or 2 when octants hold more than 32 ordinates (3D)
+  int V;               // ordinates per lane (1)
+  int sweep_variant;   // 1 = one row at a time, 2 = row pairs (two cells in flight per warp)
   int n_units;
   SweepUnit * h_units; // host copy
   int * unit_octant;   // [U]

@@ -158,7 +158,7 @@ int doma_b200_device_ptr(doma_b200_ctx * ctx, int32_t which, int32_t index, void
 enum
 {
   DOMA_INFO_KERNEL_LAUNCHES = 0, /* kernels launched by this context so far */
-  DOMA_INFO_SWEEP_VARIANT = 1,   /* 1 = persistent KBA tiles, one ordinate per lane (the only variant so far) */
+  DOMA_INFO_SWEEP_VARIANT = 1,   /* persistent KBA tiles: 1 = one row of a tile at a time, 2 = row pairs (two cells in flight per warp) */
   DOMA_INFO_N_CELLS = 2,
   DOMA_INFO_N_ORD = 3,
   DOMA_INFO_FACE_BYTES = 4,

@@ -67,8 +67,9 @@ SHAPES = [  # (shape, dims, scheme, npol, nazi, tile) incl. ragged tiles and lan
 ]
 
 
+@pytest.mark.parametrize("variant", [1, 2])
 @pytest.mark.parametrize("shape,dims,scheme,npol,nazi,tile", SHAPES)
-def test_single_sweep_matches_oracle(shape, dims, scheme, npol, nazi, tile, cuda_lib, oracle_lib):
+def test_single_sweep_matches_oracle(shape, dims, scheme, npol, nazi, tile, variant, cuda_lib, oracle_lib):
     mode = abi.MODE_TRANSIENT if dims == 2 else abi.MODE_FIXED
     prob = random_problem(shape, G=2, dims=dims, scheme=scheme, npol=npol, nazi=nazi, seed=sum(shape), mode=mode, dt=0.01)
     rng = np.random.default_rng(1)
@@ -79,6 +80,7 @@ def test_single_sweep_matches_oracle(shape, dims, scheme, npol, nazi, tile, cuda
         ctx = abi.Context(prob, lib)
         if lib is cuda_lib:
             ctx.set_tile(8, *tile)
+            ctx.set_sweep_variant(variant)
         ctx.reset_state(0.0)
         ctx.set_array(abi.ARR_Q, 0, q)
         for g in (1, 1):           # two sweeps into the same phi_cur: accumulation and epoch reuse
@@ -86,7 +88,7 @@ def test_single_sweep_matches_oracle(shape, dims, scheme, npol, nazi, tile, cuda
         out.append(ctx.get_array(abi.ARR_PHI_CUR, 0))
     assert np.all(np.isfinite(out[0])) and np.abs(out[0]).max() > 0
     assert relmax(out[1], out[0]) <= FLUX_RTOL
-    assert ctx.info(abi.INFO_SWEEP_VARIANT) == 1
+    assert ctx.info(abi.INFO_SWEEP_VARIANT) == variant
 
 
 def test_sweep_from_host_equals_resident(cuda_lib):
