@@ -130,7 +130,12 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--tile", default="", help="TYxTZ override of the KBA tile, e.g. 4x8")
     ap.add_argument("--ref-n", type=int, default=64, help="cells per axis of the bounded CPU sample")
-    ap.add_argument("--variant", type=int, default=0, help="sweep variant override (1 = row at a time, 2 = row pairs)")
+    ap.add_argument("--emulate-world", type=int, default=0,
+                    help="tuning aid, 1 GPU only: sweep rank 0's ordinate shard of a W-rank run (no all-reduce); "
+                         "the line is marked 'emulated_world' and is not a bench value")
+    ap.add_argument("--no-fused-si", action="store_true",
+                    help="drive sweep / all-reduce / residual / scattering-source update as separate ABI calls (the drop-in "
+                         "driver's sequence) instead of doma_b200_source_iteration")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     a = ap.parse_args()
@@ -181,26 +186,37 @@ def main():
     full_ord = prob.n_ord
     if world > 1:
         prob = prob.with_ordinates(shard_ordinates(prob, rank, world))
+    elif a.emulate_world > 1:
+        prob = prob.with_ordinates(shard_ordinates(prob, 0, a.emulate_world))
+        full_ord = prob.n_ord
     ctx = abi.Context(prob)
     stream = torch.cuda.Stream(device=local)
     ctx.set_stream(stream.cuda_stream)      # the context launches on this stream, so torch events see its kernels
     if a.tile:
         ty, tz = [int(v) for v in a.tile.lower().split("x")]
         ctx.set_tile(8, ty, tz)
-    if a.variant:
-        ctx.set_sweep_variant(a.variant)
     allreduce = make_allreduce(ctx) if world > 1 else None
     N = prob.n_cells
     updates_per_step = float(N) * full_ord * G
 
-    def step():
-        for g in range(G):
-            ctx.update_mg_source(g, 0.0)
+    fused = not a.no_fused_si
+
+    def one_group(g):
+        # Mode B of the synthetic case: fs_tol = 1e30, fs_max_it = 2 -> sourceIteration does exactly one sweep
+        ctx.update_mg_source(g, 0.0)
+        if fused:
+            it, _, _ = ctx.source_iteration(g, 1e30, 2)     # sweep -> NCCL all-reduce -> residual + update, in the library
+            assert it == 1
+        else:
             ctx.sweep(g)
             if allreduce is not None:
                 allreduce(ctx)
-            ctx.scatter_residual(g)
+            ctx.scatter_residual(g)      # synchronises the stream
             ctx.update_scatter_source(g)
+
+    def step():
+        for g in range(G):
+            one_group(g)
         return ctx.mg_residual()
 
     def barrier():
@@ -225,13 +241,8 @@ def main():
     # region is bracketed by stream synchronisation + barrier, so wall == device time here
     for _ in range(a.steps):
         for g in range(G):
-            ctx.update_mg_source(g, 0.0)
-            ctx.sweep(g)
-            if allreduce is not None:
-                allreduce(ctx)
-            ctx.scatter_residual(g)      # synchronises the stream
+            one_group(g)
             sweep_ms.append(ctx.last_sweep_ms())
-            ctx.update_scatter_source(g)
         ctx.mg_residual()
     ev1.record(stream)
     barrier()
@@ -317,8 +328,11 @@ def main():
            "ms_per_step": dt / a.steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
            "data": "synthetic", "config": config, "grind_ns": 1e9 / value, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
            "gpu_launches": int(launches), "clocks": clocks, "wall_ms_per_step": wall / a.steps * 1e3,
-           "tile": a.tile or "default", "sweep_variant": int(ctx.info(abi.INFO_SWEEP_VARIANT)),
-           "units_per_rank": int(ctx.info(abi.INFO_N_UNITS))}
+           "tile": "8x%dx%d%s" % (ctx.info(abi.INFO_TILE_Y), ctx.info(abi.INFO_TILE_Z), "" if a.tile else " (auto)"), "sweep_variant": int(ctx.info(abi.INFO_SWEEP_VARIANT)),
+           "units_per_rank": int(ctx.info(abi.INFO_N_UNITS)),
+           "inner_loop": "doma_b200_source_iteration (library-owned)" if fused else "separate ABI calls"}
+    if a.emulate_world > 1:
+        out["emulated_world"] = a.emulate_world
     print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()

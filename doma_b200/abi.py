@@ -26,7 +26,8 @@ SCHEME_DD, SCHEME_TWDD = 0, 1
 STEP_NONE, STEP_INSERT, STEP_REMOVE, STEP_BOTH = -1, 0, 1, 2
 MAT_HAS_SRC, MAT_HAS_CHI_P, MAT_HAS_NU_SIGMA_F = 1, 2, 4
 ARR_PHI_TOT, ARR_PHI_PREV, ARR_PHI_LAST, ARR_DNP_CUR, ARR_DNP_LAST, ARR_Q, ARR_PHI_CUR = range(7)
-INFO_KERNEL_LAUNCHES, INFO_SWEEP_VARIANT, INFO_N_CELLS, INFO_N_ORD, INFO_FACE_BYTES, INFO_DEVICE_BYTES, INFO_N_UNITS, INFO_N_TILES = range(8)
+(INFO_KERNEL_LAUNCHES, INFO_SWEEP_VARIANT, INFO_N_CELLS, INFO_N_ORD, INFO_FACE_BYTES, INFO_DEVICE_BYTES, INFO_N_UNITS, INFO_N_TILES,
+ INFO_TILE_Y, INFO_TILE_Z) = range(10)
 
 _pd = C.POINTER(C.c_double)
 _pi = C.POINTER(C.c_int32)
@@ -203,6 +204,7 @@ class Library:
         "comm_init": [C.c_void_p, C.c_int32, C.c_int32, C.c_char_p, C.c_int32],
         "allreduce_phi_cur": [C.c_void_p],
         "set_tile": [C.c_void_p, C.c_int32, C.c_int32, C.c_int32],
+        "source_iteration": [C.c_void_p, C.c_int32, C.c_double, C.c_int32, C.POINTER(C.c_int32), _pd, _pd],
     }
 
     def __init__(self, path: str = LIB_PATH, prefix: str = "doma_b200_"):
@@ -295,6 +297,13 @@ class Context:
         self._call("sweep_from_host", int(g), q_host.ctypes.data_as(_pd), phi_out.ctypes.data_as(_pd))
 
     # reductions ----------------------------------------------------------------------------------
+    def source_iteration(self, g: int, tol: float, max_it: int):
+        """sourceIteration(g) as one call; returns (iterations, last residual, residual of every iteration)."""
+        it, res = C.c_int32(0), C.c_double(0.0)
+        hist = np.zeros(max(int(max_it), 1), dtype=np.float64)
+        self._call("source_iteration", int(g), float(tol), int(max_it), C.byref(it), C.byref(res), hist.ctypes.data_as(_pd))
+        return int(it.value), float(res.value), hist[:int(it.value)]
+
     def scatter_residual(self, g: int) -> float:
         out = C.c_double()
         self._call("scatter_residual", int(g), C.byref(out))

@@ -9,10 +9,6 @@
 
 #include <vector>
 
-#ifndef DOMA_DEFAULT_VARIANT
-#define DOMA_DEFAULT_VARIANT 1
-#endif
-
 namespace
 {
 char g_create_err[DOMA_MAX_ERR] = "";
@@ -137,8 +133,32 @@ doma_build_units(doma_b200_ctx * c, int V)
     c->face_bytes = sizeof(double) * (nfx + nfy + nfz);
     c->device_bytes += c->face_bytes;
   }
-  // default tile: 8 x 4 x 8 in 3D, 8 x 4 in 2D
-  return doma_sweep_setup_tiles(c, c->tile_y > 0 ? c->tile_y : 4, c->dims == 3 ? (c->tile_z > 0 ? c->tile_z : 8) : 1);
+  if (c->tile_y > 0 && c->tile_z > 0)
+    return doma_sweep_setup_tiles(c, c->tile_y, c->dims == 3 ? c->tile_z : 1); // keep a tile the caller chose
+  // Default tile: the largest of 8x4x8, 8x4x4, 8x4x2, 8x2x2 (2D: 8x4, 8x2, 8x1) that still keeps every resident
+  // warp busy.  A big tile amortises the per-task cost (flag polls, fence, face rows) but a sweep unit only
+  // exposes n_tiles / n_hyperplanes independent tiles on average; with few units per GPU (angle sharding over
+  // 4-8 ranks, or 16 ordinates per octant) the wavefront starves.  Measured on B200 at 256^3 (profiles/
+  // r01_sweep_experiments.txt): 16 and 8 units -> 8x4x8, 4 units -> 8x4x4, 2 units -> 8x4x2.
+  static const int cand3[][2] = {{4, 8}, {4, 4}, {4, 2}, {2, 2}};
+  static const int cand2[][2] = {{4, 1}, {2, 1}, {1, 1}};
+  const int(*cand)[2] = c->dims == 3 ? cand3 : cand2;
+  const int n_cand = c->dims == 3 ? 4 : 3;
+  const double want = 16.0 * c->n_sms; // resident warps: 4 CTAs x 4 warps per SM
+  int pick = n_cand - 1;
+  for (int i = 0; i < n_cand; ++i)
+  {
+    const double ntx = (c->nx + 7) / 8, nty = (c->ny + cand[i][0] - 1) / cand[i][0], ntz = (c->nz + cand[i][1] - 1) / cand[i][1];
+    const double in_flight = (double)(c->n_units > 0 ? c->n_units : 1) * ntx * nty * ntz / (ntx + nty + ntz - 2.0);
+    if (in_flight >= want)
+    {
+      pick = i;
+      break;
+    }
+  }
+  rc = doma_sweep_setup_tiles(c, cand[pick][0], cand[pick][1]);
+  c->tile_auto = true;
+  return rc;
 }
 
 namespace
@@ -257,10 +277,6 @@ create_impl(doma_b200_ctx * c, const doma_b200_problem * p)
     }
     (void)per_oct;
     DOMA_CUDA(c, cudaMalloc(&c->work_counter, sizeof(int)));
-    c->sweep_variant = DOMA_DEFAULT_VARIANT;
-    if (const char * v = getenv("DOMA_B200_SWEEP_VARIANT"))
-      if (atoi(v) == 1 || atoi(v) == 2)
-        c->sweep_variant = atoi(v);
     if ((rc = doma_build_units(c, 1)))
       return rc;
   }
@@ -470,6 +486,40 @@ doma_b200_sweep_from_host(doma_b200_ctx * c, int32_t g, const double * q_host, d
   return 0;
 }
 
+// sourceIteration(g) (3D:458-497) owned by the library: no host round trip between the sweep, the all-reduce
+// and the residual/update pass; one 16-byte readback per iteration for the loop condition.
+int
+doma_b200_source_iteration(doma_b200_ctx * c, int32_t g, double tol, int32_t max_it, int32_t * iters_out, double * residual_out,
+                           double * residual_history)
+{
+  ENTER(c);
+  CHECK_GROUP(c, g);
+  if (!iters_out || !residual_out)
+  {
+    snprintf(c->err, DOMA_MAX_ERR, "source_iteration: null output pointer");
+    return 1;
+  }
+  int32_t it = 0;
+  double res = 0.0;
+  do
+  {
+    int rc = doma_launch_sweep(c, g);
+    if (rc)
+      return rc;
+    if (c->nccl_comm && (rc = doma_b200_allreduce_phi_cur(c)))
+      return rc;
+    if ((rc = doma_launch_scatter_residual_update(c, g)))
+      return rc;
+    res = c->h_red[1] > 1e-8 ? sqrt(c->h_red[0]) / sqrt(c->h_red[1]) : 0.0; // 3D:562
+    if (residual_history)
+      residual_history[it] = res;
+    it++;
+  } while (it < max_it && tol < res);
+  *iters_out = it;
+  *residual_out = res;
+  return 0;
+}
+
 int
 doma_b200_scatter_residual(doma_b200_ctx * c, int32_t g, double * out)
 {
@@ -577,13 +627,15 @@ doma_b200_get_info(doma_b200_ctx * c, int32_t what, int64_t * out)
   switch (what)
   {
     case DOMA_INFO_KERNEL_LAUNCHES: *out = c->launches; break;
-    case DOMA_INFO_SWEEP_VARIANT: *out = c->sweep_variant; break;
+    case DOMA_INFO_SWEEP_VARIANT: *out = c->V; break;
     case DOMA_INFO_N_CELLS: *out = c->N; break;
     case DOMA_INFO_N_ORD: *out = c->n_ord; break;
     case DOMA_INFO_FACE_BYTES: *out = c->face_bytes; break;
     case DOMA_INFO_DEVICE_BYTES: *out = c->device_bytes; break;
     case DOMA_INFO_N_UNITS: *out = c->n_units; break;
     case DOMA_INFO_N_TILES: *out = c->n_tiles; break;
+    case DOMA_INFO_TILE_Y: *out = c->tile_y; break;
+    case DOMA_INFO_TILE_Z: *out = c->tile_z; break;
     default: snprintf(c->err, DOMA_MAX_ERR, "get_info: unknown item %d", what); return 4;
   }
   return 0;
@@ -593,14 +645,14 @@ int
 doma_b200_set_sweep_variant(doma_b200_ctx * c, int32_t variant)
 {
   ENTER(c);
-  if (variant != 1 && variant != 2)
+  if (variant != 1)
   {
-    snprintf(c->err, DOMA_MAX_ERR, "set_sweep_variant: variants are 1 (one row at a time) and 2 (row pairs), got %d", variant);
+    snprintf(c->err, DOMA_MAX_ERR, "set_sweep_variant: only variant 1 (persistent KBA tiles, one ordinate per lane) exists");
     return 4;
   }
-  DOMA_CUDA(c, cudaStreamSynchronize(c->stream));
-  c->sweep_variant = variant;
-  return 0;
+  if (variant == c->V)
+    return 0;
+  return doma_build_units(c, variant);
 }
 
 int

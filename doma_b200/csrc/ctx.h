@@ -52,8 +52,7 @@ struct doma_b200_ctx
   // into sweep units (octant x V batches of <=32 ordinates), lane-major
   int32_t * h_ord_octant;
   double *h_mu, *h_eta, *h_xi, *h_w; // [n_ord] signed, as passed in
-  int V;               // ordinates per lane (1)
-  int sweep_variant;   // 1 = one row at a time, 2 = row pairs (two cells in flight per warp)
+  int V;               // ordinates per lane: 1, or 2 when octants hold more than 32 ordinates (3D)
   int n_units;
   SweepUnit * h_units; // host copy
   int * unit_octant;   // [U]
@@ -61,6 +60,7 @@ struct doma_b200_ctx
 
   // sweep scratch
   int tile_x, tile_y, tile_z; // tile_x is fixed to 8 by the kernel (row held in registers)
+  bool tile_auto;             // tile chosen by the library's occupancy heuristic (api.cu), not by set_tile
   int ntx, nty, ntz, n_tiles;
   uint32_t * tile_order; // [n_tiles] packed (I',J',K') sorted by I'+J'+K'
   double *face_x, *face_y, *face_z; // [U][nz][ny][32V], [U][nz][nx][32V], [U][ny][nx][32V]
@@ -106,6 +106,7 @@ int doma_launch_update_mg_source(doma_b200_ctx * c, int g, double t);
 int doma_launch_update_mg_source_eigen(doma_b200_ctx * c, int g, double k);
 int doma_launch_update_scatter_source(doma_b200_ctx * c, int g);
 int doma_launch_scatter_residual(doma_b200_ctx * c, int g); // leaves (diff, total) in h_red after sync
+int doma_launch_scatter_residual_update(doma_b200_ctx * c, int g); // fused pair, leaves (diff, total) in h_red
 int doma_launch_mg_residual(doma_b200_ctx * c);
 int doma_launch_k_sums(doma_b200_ctx * c, double k);
 int doma_launch_sig_eff(doma_b200_ctx * c, int g);

@@ -78,7 +78,9 @@ step_dnps_kernel(int64_t N, int G, int D, double dt, const int32_t * __restrict_
   }
 }
 
-// updateMultigroupSource(g,t) (3D:339-402)
+// updateMultigroupSource(g,t) (3D:339-402).  GT = compile-time group count (1..8; 0 = run-time G): the G
+// loads of phi_tot are issued up front instead of one per iteration behind an IEEE division.
+template <int GT>
 __global__ void
 mg_source_kernel(int64_t N, int G, int D, int g, double t, double f, int transient, double dt,
                  const int32_t * __restrict__ mat, const int32_t * __restrict__ mat_flags,
@@ -97,6 +99,13 @@ mg_source_kernel(int64_t N, int G, int D, int g, double t, double f, int transie
   const int nd = n_delayed[m];
   const bool has_chi = (mat_flags[m] & DOMA_MAT_HAS_CHI_P) != 0;
   phi_cur[i] = 0.0;
+  double ph[GT > 0 ? GT : 1];
+  if (GT > 0)
+  {
+#pragma unroll
+    for (int gp = 0; gp < GT; ++gp)
+      ph[gp] = phi_tot[gp * N + i];
+  }
   double q = (mat_flags[m] & DOMA_MAT_HAS_SRC) ? f * src[m * G + g] / M_PI : 0.0;
   if (transient && step_type[m] != DOMA_STEP_NONE)
   {
@@ -109,12 +118,19 @@ mg_source_kernel(int64_t N, int G, int D, int g, double t, double f, int transie
       default: break;
     }
   }
-  for (int gp = 0; gp < G; ++gp)
+#pragma unroll
+  for (int gp = 0; gp < (GT > 0 ? GT : G); ++gp)
   {
-    const double phi = phi_tot[gp * N + i];
-    if (gp != g)
-      q += f * sigma_s[(m * G + g) * G + gp] * phi / M_PI;
-    if (has_chi && nd == 0)
+    const double phi = GT > 0 ? ph[gp] : phi_tot[gp * N + i];
+    // A term whose cross section is exactly zero adds +-0 and leaves q unchanged (for finite phi), so its
+    // IEEE division is skipped: the common case for the up-scatter half of sigma_s and for chi_p = 0.
+    const double ss = sigma_s[(m * G + g) * G + gp];
+    if (gp != g && ss != 0.0)
+      q += f * ss * phi / M_PI;
+    const double chi = has_chi ? chi_p[m * G + g] : 0.0, nsf = has_chi ? nu_sigma_f[m * G + gp] : 0.0;
+    if (chi == 0.0 || nsf == 0.0)
+      ;
+    else if (has_chi && nd == 0)
       q += f * chi_p[m * G + g] * nu_sigma_f[m * G + gp] * phi / M_PI;
     else if (has_chi && nd > 0)
     {
@@ -136,6 +152,7 @@ mg_source_kernel(int64_t N, int G, int D, int g, double t, double f, int transie
 }
 
 // updateMultigroupSourceEigen(g) (3D:404-430): "+=" onto the stale q
+template <int GT>
 __global__ void
 mg_source_eigen_kernel(int64_t N, int G, int g, double k, double f, const int32_t * __restrict__ mat,
                        const int32_t * __restrict__ mat_flags, const double * __restrict__ sigma_s,
@@ -149,13 +166,22 @@ mg_source_eigen_kernel(int64_t N, int G, int g, double k, double f, const int32_
   const int m = mat[i];
   const bool has_chi = (mat_flags[m] & DOMA_MAT_HAS_CHI_P) != 0;
   phi_cur[i] = 0.0;
-  double q = q_io[i];
-  for (int gp = 0; gp < G; ++gp)
+  double ph[GT > 0 ? GT : 1];
+  if (GT > 0)
   {
-    const double phi = phi_tot[gp * N + i];
-    if (gp != g)
-      q += f * sigma_s[(m * G + g) * G + gp] * phi / M_PI;
-    if (has_chi)
+#pragma unroll
+    for (int gp = 0; gp < GT; ++gp)
+      ph[gp] = phi_tot[gp * N + i];
+  }
+  double q = q_io[i];
+#pragma unroll
+  for (int gp = 0; gp < (GT > 0 ? GT : G); ++gp)
+  {
+    const double phi = GT > 0 ? ph[gp] : phi_tot[gp * N + i];
+    const double ss = sigma_s[(m * G + g) * G + gp]; // exact zeros skipped, see mg_source_kernel
+    if (gp != g && ss != 0.0)
+      q += f * ss * phi / M_PI;
+    if (has_chi && chi_p[m * G + g] != 0.0 && nu_sigma_f[m * G + gp] != 0.0)
       q += f * chi_p[m * G + g] * nu_sigma_f[m * G + gp] * phi / M_PI / k;
   }
   q_io[i] = q;
@@ -238,6 +264,29 @@ scatter_residual_kernel(int64_t N, Geo geo, const double * __restrict__ phi_tot_
     const double cur = phi_cur[i], s = phi_tot_g[i] + cur;
     diff = diff + (cur * cur) * v;
     total = total + (s * s) * v;
+  }
+  block_reduce2(diff, total, partial, blockIdx.x);
+}
+
+// computeScatteringResidual(g) immediately followed by updateScatteringSource(g), as sourceIteration always
+// calls them (3D:475-477), in ONE pass over the cells: same per-cell expressions, same grid and reduction
+// order as the two separate kernels, so residual and state are bit-identical to the unfused path.
+// 16 B read + 24 B written per cell instead of 32 B + 24 B.
+__global__ void
+scatter_residual_update_kernel(int64_t N, int G, int g, double f, Geo geo, const int32_t * __restrict__ mat,
+                               const double * __restrict__ sigma_s, double * __restrict__ phi_tot_g,
+                               double * __restrict__ phi_cur, double * __restrict__ q, double * __restrict__ partial)
+{
+  double diff = 0.0, total = 0.0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < N; i += (int64_t)gridDim.x * blockDim.x)
+  {
+    const double v = geo.measure(i);
+    const double cur = phi_cur[i], s = phi_tot_g[i] + cur;
+    diff = diff + (cur * cur) * v;
+    total = total + (s * s) * v;
+    phi_tot_g[i] = s;
+    q[i] = f * sigma_s[(mat[i] * G + g) * G + g] * cur / M_PI;
+    phi_cur[i] = 0.0;
   }
   block_reduce2(diff, total, partial, blockIdx.x);
 }
@@ -372,10 +421,24 @@ doma_launch_update_mg_source(doma_b200_ctx * c, int g, double t)
 {
   const double f = c->dims == 3 ? 0.25 : 0.5;
   const int transient = c->mode == DOMA_MODE_TRANSIENT;
-  mg_source_kernel<<<ew_blocks(c->N), EW_THREADS, 0, c->stream>>>(
-      c->N, c->G, c->D, g, t, f, transient, c->dt, c->mat, c->mat_flags, c->n_delayed, c->step_type, c->step_t_insert,
-      c->step_t_remove, c->step_src, c->src, c->sigma_s, c->chi_p, c->nu_sigma_f, c->beta, c->chi_d, c->lambda, c->inv_v,
-      c->dnp_cur, c->phi_last, c->phi_tot, c->phi_prev, c->q, c->phi_cur);
+#define MGS(GT)                                                                                                          \
+  mg_source_kernel<GT><<<ew_blocks(c->N), EW_THREADS, 0, c->stream>>>(                                                   \
+      c->N, c->G, c->D, g, t, f, transient, c->dt, c->mat, c->mat_flags, c->n_delayed, c->step_type, c->step_t_insert, \
+      c->step_t_remove, c->step_src, c->src, c->sigma_s, c->chi_p, c->nu_sigma_f, c->beta, c->chi_d, c->lambda,        \
+      c->inv_v, c->dnp_cur, c->phi_last, c->phi_tot, c->phi_prev, c->q, c->phi_cur)
+  switch (c->G)
+  {
+    case 1: MGS(1); break;
+    case 2: MGS(2); break;
+    case 3: MGS(3); break;
+    case 4: MGS(4); break;
+    case 5: MGS(5); break;
+    case 6: MGS(6); break;
+    case 7: MGS(7); break;
+    case 8: MGS(8); break;
+    default: MGS(0); break;
+  }
+#undef MGS
   c->launches += 1;
   DOMA_CUDA(c, cudaGetLastError());
   return 0;
@@ -385,9 +448,23 @@ int
 doma_launch_update_mg_source_eigen(doma_b200_ctx * c, int g, double k)
 {
   const double f = c->dims == 3 ? 0.25 : 0.5;
-  mg_source_eigen_kernel<<<ew_blocks(c->N), EW_THREADS, 0, c->stream>>>(c->N, c->G, g, k, f, c->mat, c->mat_flags, c->sigma_s,
-                                                                        c->chi_p, c->nu_sigma_f, c->phi_tot, c->phi_prev, c->q,
-                                                                        c->phi_cur);
+#define MGE(GT)                                                                                                    \
+  mg_source_eigen_kernel<GT><<<ew_blocks(c->N), EW_THREADS, 0, c->stream>>>(c->N, c->G, g, k, f, c->mat, c->mat_flags, \
+                                                                            c->sigma_s, c->chi_p, c->nu_sigma_f,     \
+                                                                            c->phi_tot, c->phi_prev, c->q, c->phi_cur)
+  switch (c->G)
+  {
+    case 1: MGE(1); break;
+    case 2: MGE(2); break;
+    case 3: MGE(3); break;
+    case 4: MGE(4); break;
+    case 5: MGE(5); break;
+    case 6: MGE(6); break;
+    case 7: MGE(7); break;
+    case 8: MGE(8); break;
+    default: MGE(0); break;
+  }
+#undef MGE
   c->launches += 1;
   DOMA_CUDA(c, cudaGetLastError());
   return 0;
@@ -409,6 +486,17 @@ doma_launch_scatter_residual(doma_b200_ctx * c, int g)
 {
   scatter_residual_kernel<<<RED_BLOCKS, EW_THREADS, 0, c->stream>>>(c->N, geo_of(c), c->phi_tot + (int64_t)g * c->N, c->phi_cur,
                                                                     c->red_partial);
+  DOMA_CUDA(c, cudaGetLastError());
+  return finish_reduce(c);
+}
+
+int
+doma_launch_scatter_residual_update(doma_b200_ctx * c, int g)
+{
+  const double f = c->dims == 3 ? 0.25 : 0.5;
+  scatter_residual_update_kernel<<<RED_BLOCKS, EW_THREADS, 0, c->stream>>>(c->N, c->G, g, f, geo_of(c), c->mat, c->sigma_s,
+                                                                           c->phi_tot + (int64_t)g * c->N, c->phi_cur, c->q,
+                                                                           c->red_partial);
   DOMA_CUDA(c, cudaGetLastError());
   return finish_reduce(c);
 }

@@ -35,7 +35,8 @@ class Trace:
 
 class TransportSolver:
     def __init__(self, ctx: abi.Context, params: InputParameters, verbose: bool = False,
-                 allreduce: Optional[Callable[[abi.Context], None]] = None, log: Callable[[str], None] = None):
+                 allreduce: Optional[Callable[[abi.Context], None]] = None, log: Callable[[str], None] = None,
+                 fused_si: bool = False):
         self.ctx = ctx
         self.num_groups = params.num_groups
         self.mode = params.mode
@@ -45,6 +46,9 @@ class TransportSolver:
         self.t0, self.dt, self.t_steps, self.ic = params.t0, params.dt, params.num_steps, params.ic
         self.verbose = verbose
         self.allreduce = allreduce       # sums phi_cur over ranks after each sweep (angle sharding)
+        # fused_si: sourceIteration runs inside the library (one ABI call per group).  Only when the
+        # all-reduce is the library's own NCCL one (or there is a single rank): a host-side hook cannot be fused.
+        self.fused_si = bool(fused_si) and ctx.has("source_iteration") and (allreduce is None or ctx.has("comm_init"))
         self.trace = Trace()
         self._log = log or (lambda s: None)
 
@@ -60,6 +64,8 @@ class TransportSolver:
 
     # --- sourceIteration (3D:458-497) ------------------------------------------------------------
     def source_iteration(self, g: int) -> bool:
+        if self.fused_si:
+            return self._source_iteration_fused(g)
         it, res = 0, 0.0
         while True:
             if self.verbose:
@@ -70,6 +76,20 @@ class TransportSolver:
             it += 1
             if not (it < self.smi and self.sit < res):
                 break
+        self.trace.si_counts.append(it)
+        self.trace.si_residuals.append(res)
+        ok = it < self.smi
+        self._log(f"SI {'converged' if ok else 'failed to converge'} after {it} iterations with a residual of {res!r} for G{g}")
+        return ok
+
+    def _source_iteration_fused(self, g: int) -> bool:
+        """The same loop owned by the library (doma_b200_source_iteration): sweep, all-reduce, residual and
+        scattering-source update without returning to the host in between; prints replayed from the history."""
+        it, res, hist = self.ctx.source_iteration(g, self.sit, self.smi)
+        if self.verbose:
+            for i in range(it):
+                self._log(f"Performing SI {i} for G{g}" + (f", residual = {hist[i - 1]!r}" if i else ""))
+        self.trace.sweeps += it
         self.trace.si_counts.append(it)
         self.trace.si_residuals.append(res)
         ok = it < self.smi

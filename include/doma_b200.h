@@ -121,6 +121,16 @@ int doma_b200_sweep(doma_b200_ctx * ctx, int32_t g);
  * cell order) to the device, zeroes phi_cur, sweeps, copies phi_cur back into phi_cur_out. Synchronous. */
 int doma_b200_sweep_from_host(doma_b200_ctx * ctx, int32_t g, const double * q_host, double * phi_cur_out);
 
+/* sourceIteration(g) (3D:458-497) as ONE call (the fused inner iteration of SURVEY.md 8f-1):
+ *   do { sweep(g); all-reduce phi_cur over ranks; residual = computeScatteringResidual(g); updateScatteringSource(g); it++ }
+ *   while (it < max_it && tol < residual);
+ * with the residual and the scattering-source update fused into one pass over the cells (identical values).
+ * iters_out = iterations executed, residual_out = the last residual; the caller applies the reference's
+ * "converged = iters < max_it" (3D:481).  residual_history (may be NULL, else >= max_it doubles) receives the
+ * residual of every iteration, for the reference's --verbose trace. */
+int doma_b200_source_iteration(doma_b200_ctx * ctx, int32_t g, double tol, int32_t max_it, int32_t * iters_out,
+                               double * residual_out, double * residual_history);
+
 /* angle sharding across ranks (one process per GPU): the scalar-flux increment is summed once per
  * sweep with an in-place ncclAllReduce(phi_cur, N, ncclDouble, ncclSum) on the context's stream
  * (replaces the serial thread-sum of 3D:609-621).  Rank 0 creates the 128-byte NCCL unique id, the
@@ -158,18 +168,21 @@ int doma_b200_device_ptr(doma_b200_ctx * ctx, int32_t which, int32_t index, void
 enum
 {
   DOMA_INFO_KERNEL_LAUNCHES = 0, /* kernels launched by this context so far */
-  DOMA_INFO_SWEEP_VARIANT = 1,   /* persistent KBA tiles: 1 = one row of a tile at a time, 2 = row pairs (two cells in flight per warp) */
+  DOMA_INFO_SWEEP_VARIANT = 1,   /* 1 = persistent KBA tiles, one ordinate per lane (the only variant so far) */
   DOMA_INFO_N_CELLS = 2,
   DOMA_INFO_N_ORD = 3,
   DOMA_INFO_FACE_BYTES = 4,
   DOMA_INFO_DEVICE_BYTES = 5,
   DOMA_INFO_N_UNITS = 6,         /* sweep units = (octant, batch of <= 32 ordinates) */
-  DOMA_INFO_N_TILES = 7          /* tiles of the KBA decomposition */
+  DOMA_INFO_N_TILES = 7,         /* tiles of the KBA decomposition */
+  DOMA_INFO_TILE_Y = 8,          /* tile extents in cells (x extent is 8); chosen by the library unless set_tile was called */
+  DOMA_INFO_TILE_Z = 9
 };
 int doma_b200_get_info(doma_b200_ctx * ctx, int32_t what, int64_t * out);
 /* select the sweep implementation (see DOMA_INFO_SWEEP_VARIANT); default 1 */
 int doma_b200_set_sweep_variant(doma_b200_ctx * ctx, int32_t variant);
-/* KBA tile extents in cells; tx must be 8 (the row a warp keeps in registers), ty <= 4. Rebuilds the tile table. */
+/* KBA tile extents in cells; tx must be 8 (the row a warp keeps in registers), ty <= 4. Rebuilds the tile table.
+ * Without this call the library picks the tile from the mesh size and the number of sweep units (api.cu). */
 int doma_b200_set_tile(doma_b200_ctx * ctx, int32_t tx, int32_t ty, int32_t tz);
 /* device time in ms of the most recent doma_b200_sweep (CUDA events on the context's stream; synchronises) */
 int doma_b200_last_sweep_ms(doma_b200_ctx * ctx, float * out);

@@ -369,6 +369,29 @@ doma_oracle_scatter_residual(doma_oracle_ctx * c, int32_t g, double * out)
   return 0;
 }
 
+int doma_oracle_sweep(doma_oracle_ctx * c, int32_t g);
+
+/* sourceIteration(g) (3D:458-497): do { sweep; residual; update } while (it < max_it && tol < residual) */
+int
+doma_oracle_source_iteration(doma_oracle_ctx * c, int32_t g, double tol, int32_t max_it, int32_t * iters_out,
+                             double * residual_out, double * residual_history)
+{
+  int32_t it = 0;
+  double res = 0.0;
+  do
+  {
+    doma_oracle_sweep(c, g);
+    doma_oracle_scatter_residual(c, g, &res);
+    doma_oracle_update_scatter_source(c, g);
+    if (residual_history)
+      residual_history[it] = res;
+    it++;
+  } while (it < max_it && tol < res);
+  *iters_out = it;
+  *residual_out = res;
+  return 0;
+}
+
 /* computeMGFluxResidual() (3D:318-337) */
 int
 doma_oracle_mg_residual(doma_oracle_ctx * c, double * out)

@@ -22,13 +22,13 @@ FLUX_RTOL = 1e-10
 K_TOL = 1e-9
 
 
-def check_against_digest(name, lib):
+def check_against_digest(name, lib, fused_si=False):
     g = np.load(os.path.join(FULL, name + ".npz"))
     params, prob = d.load_case(golden_case_path("full_" + name))
     assert [prob.nx, prob.ny, prob.nz if prob.dims == 3 else 1] == g["shape"].tolist()
     assert prob.n_ord == int(g["n_ord"])
     ctx = abi.Context(prob, lib)
-    s = d.TransportSolver(ctx, params)
+    s = d.TransportSolver(ctx, params, fused_si=fused_si)
     ok = s.solve()
     assert ok == bool(g["ok"])
     assert list(s.trace.si_counts) == list(g["si_counts"]), "source-iteration trace differs from the reference"
@@ -59,9 +59,10 @@ def check_against_digest(name, lib):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("fused_si", [False, True], ids=["loop_on_host", "fused_si"])
 @pytest.mark.parametrize("name", NAMES)
-def test_shipped_case_matches_reference_digest(name, cuda_lib):
-    ctx = check_against_digest(name, cuda_lib)
+def test_shipped_case_matches_reference_digest(name, fused_si, cuda_lib):
+    ctx = check_against_digest(name, cuda_lib, fused_si)
     assert ctx.info(abi.INFO_KERNEL_LAUNCHES) > 0
 
 

@@ -24,18 +24,21 @@ def relmax(a, b):
     return float(np.max(np.abs(a - b) / np.maximum(np.abs(b), 1e-300)))
 
 
-def solve(name, lib):
+def solve(name, lib, fused_si=False):
     params, prob = d.load_case(golden_case_path(name))
     ctx = abi.Context(prob, lib)
-    s = d.TransportSolver(ctx, params)
+    s = d.TransportSolver(ctx, params, fused_si=fused_si)
+    assert s.fused_si == fused_si
     ok = s.solve()
     return params, prob, ctx, s, ok
 
 
+@pytest.mark.parametrize("fused_si", [False, True], ids=["loop_on_host", "fused_si"])
 @pytest.mark.parametrize("name", golden_names())
-def test_cuda_matches_reference_golden(name, cuda_lib):
+def test_cuda_matches_reference_golden(name, fused_si, cuda_lib):
+    """fused_si: sourceIteration owned by the library (doma_b200_source_iteration)."""
     g = load_golden(name)
-    params, prob, ctx, s, ok = solve(name, cuda_lib)
+    params, prob, ctx, s, ok = solve(name, cuda_lib, fused_si)
     assert ok == bool(g["ok"])
     assert list(s.trace.si_counts) == list(g["si_counts"]), "source-iteration trace differs from the reference"
     phi = s.flux()
@@ -67,9 +70,8 @@ SHAPES = [  # (shape, dims, scheme, npol, nazi, tile) incl. ragged tiles and lan
 ]
 
 
-@pytest.mark.parametrize("variant", [1, 2])
 @pytest.mark.parametrize("shape,dims,scheme,npol,nazi,tile", SHAPES)
-def test_single_sweep_matches_oracle(shape, dims, scheme, npol, nazi, tile, variant, cuda_lib, oracle_lib):
+def test_single_sweep_matches_oracle(shape, dims, scheme, npol, nazi, tile, cuda_lib, oracle_lib):
     mode = abi.MODE_TRANSIENT if dims == 2 else abi.MODE_FIXED
     prob = random_problem(shape, G=2, dims=dims, scheme=scheme, npol=npol, nazi=nazi, seed=sum(shape), mode=mode, dt=0.01)
     rng = np.random.default_rng(1)
@@ -80,7 +82,6 @@ def test_single_sweep_matches_oracle(shape, dims, scheme, npol, nazi, tile, vari
         ctx = abi.Context(prob, lib)
         if lib is cuda_lib:
             ctx.set_tile(8, *tile)
-            ctx.set_sweep_variant(variant)
         ctx.reset_state(0.0)
         ctx.set_array(abi.ARR_Q, 0, q)
         for g in (1, 1):           # two sweeps into the same phi_cur: accumulation and epoch reuse
@@ -88,7 +89,7 @@ def test_single_sweep_matches_oracle(shape, dims, scheme, npol, nazi, tile, vari
         out.append(ctx.get_array(abi.ARR_PHI_CUR, 0))
     assert np.all(np.isfinite(out[0])) and np.abs(out[0]).max() > 0
     assert relmax(out[1], out[0]) <= FLUX_RTOL
-    assert ctx.info(abi.INFO_SWEEP_VARIANT) == variant
+    assert ctx.info(abi.INFO_SWEEP_VARIANT) == 1
 
 
 def test_sweep_from_host_equals_resident(cuda_lib):
@@ -106,14 +107,17 @@ def test_sweep_from_host_equals_resident(cuda_lib):
 
 def test_elementwise_kernels_bit_identical(cuda_lib, oracle_lib):
     """Source build / update / DNP step: same per-cell arithmetic, no FMA -> identical bits."""
-    for dims, mode, D in ((3, abi.MODE_FIXED, 0), (3, abi.MODE_EIGEN, 0), (2, abi.MODE_TRANSIENT, 3), (3, abi.MODE_TRANSIENT, 2)):
+    # G = 9 takes the kernels' run-time group loop (groups 1..8 are compile-time specialisations)
+    for dims, mode, D, G in ((3, abi.MODE_FIXED, 0, 3), (3, abi.MODE_EIGEN, 0, 3), (2, abi.MODE_TRANSIENT, 3, 3),
+                             (3, abi.MODE_TRANSIENT, 2, 3), (3, abi.MODE_FIXED, 0, 9), (3, abi.MODE_EIGEN, 0, 9)):
         shape = (11, 6, 4) if dims == 3 else (15, 9, 1)
-        prob = random_problem(shape, G=3, dims=dims, mode=mode, D=D, dt=0.02, seed=dims * 10 + mode)
+        prob = random_problem(shape, G=G, dims=dims, mode=mode, D=D, dt=0.02, seed=dims * 10 + mode)
         prob.step_type[1] = abi.STEP_BOTH
         prob.step_t_remove[1] = 0.5
-        prob.step_src[1] = [3.0, 0.0, 1.0]
+        prob.step_src[1] = ([3.0, 0.0, 1.0] * 3)[:G]
+        prob.sigma_s[:, 2, 0] = 0.0                     # exact zeros ([to, from]): the kernels skip those terms
         rng = np.random.default_rng(3)
-        N, G = prob.n_cells, 3
+        N = prob.n_cells
         state = {(abi.ARR_PHI_TOT, g): rng.uniform(0, 5, N) for g in range(G)}
         state.update({(abi.ARR_PHI_PREV, g): rng.uniform(0, 5, N) for g in range(G)})
         state[(abi.ARR_Q, 0)] = rng.uniform(0, 1, N)
