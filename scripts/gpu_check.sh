@@ -7,7 +7,7 @@ timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -5
 python bench.py ${BENCH_ARGS:-} > gpurun_out/bench.json 2> gpurun_out/bench.err; tail -c 3000 gpurun_out/bench.json; tail -5 gpurun_out/bench.err
 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/bench_ref.json 2>> gpurun_out/bench.err; cat gpurun_out/bench_ref.json
 if [ -n "$DO_NCU" ]; then
-  P="python bench.py --n 128 --steps 1 --warmup 3 --no-cpu-baseline --no-e2e"
+  P="python bench.py --n ${NCU_N:-128} --steps 1 --warmup 3 --no-cpu-baseline --no-e2e"
   $P > gpurun_out/plain.log 2>&1 &&
   ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv $P > gpurun_out/ncu_list.log 2>&1
   $P > gpurun_out/plain2.log 2>&1 &&
