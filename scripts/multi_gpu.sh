@@ -3,9 +3,10 @@
 N=${1:-2}; shift
 mkdir -p gpurun_out
 nvidia-smi topo -m 2>/dev/null | head -12 > gpurun_out/topo_n$N.txt
-for tile in ${TILES:-4x8}; do
+for tile in ${TILES:-auto}; do
+  if [ "$tile" = auto ]; then TF=""; else TF="--tile $tile"; fi
   python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 \
-    bench.py --gpus $N --steps ${STEPS:-3} --warmup 3 --tile $tile "$@" 2> gpurun_out/mg_n${N}_$tile.err | tail -1 > gpurun_out/mg_n${N}_$tile.json
+    bench.py --gpus $N --steps ${STEPS:-3} --warmup 3 $TF "$@" 2> gpurun_out/mg_n${N}_$tile.err | tail -1 > gpurun_out/mg_n${N}_$tile.json
   python - <<PY
 import json
 try:
