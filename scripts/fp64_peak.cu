@@ -7,7 +7,8 @@
 #include <cuda_runtime.h>
 #include <stdio.h>
 
-template <int ILP>
+// OP: 0 = DFMA, 1 = DADD, 2 = DMUL, 3 = DMUL then DADD alternating (same chain)
+template <int ILP, int OP = 0>
 __global__ void __launch_bounds__(1024, 1)
 dfma_kernel(double * out, int iters, double a, double b)
 {
@@ -21,7 +22,7 @@ dfma_kernel(double * out, int iters, double a, double b)
     for (int r = 0; r < 16; ++r)
 #pragma unroll
       for (int i = 0; i < ILP; ++i)
-        x[i] = fma(x[i], a, b);
+        x[i] = OP == 0 ? fma(x[i], a, b) : OP == 1 ? __dadd_rn(x[i], b) : OP == 2 ? __dmul_rn(x[i], a) : ((r & 1) ? __dadd_rn(x[i], b) : __dmul_rn(x[i], a));
   }
   double s = 0.0;
 #pragma unroll
@@ -31,7 +32,7 @@ dfma_kernel(double * out, int iters, double a, double b)
     out[0] = s;
 }
 
-template <int ILP>
+template <int ILP, int OP = 0>
 double
 run(int warps_per_sm, int n_sms, double * d_out, double * inst_per_clk_sm, int clock_khz)
 {
@@ -39,10 +40,10 @@ run(int warps_per_sm, int n_sms, double * d_out, double * inst_per_clk_sm, int c
   cudaEvent_t e0, e1;
   cudaEventCreate(&e0);
   cudaEventCreate(&e1);
-  dfma_kernel<ILP><<<n_sms, warps_per_sm * 32>>>(d_out, 64, 0.999999, 1e-9);
+  dfma_kernel<ILP, OP><<<n_sms, warps_per_sm * 32>>>(d_out, 64, 0.999999, 1e-9);
   cudaDeviceSynchronize();
   cudaEventRecord(e0);
-  dfma_kernel<ILP><<<n_sms, warps_per_sm * 32>>>(d_out, iters, 0.999999, 1e-9);
+  dfma_kernel<ILP, OP><<<n_sms, warps_per_sm * 32>>>(d_out, iters, 0.999999, 1e-9);
   cudaEventRecord(e1);
   cudaEventSynchronize(e1);
   float ms = 0.f;
@@ -75,6 +76,19 @@ main()
   if (tf > best)                                                   \
     best = tf;
     RUN(1) RUN(2) RUN(3) RUN(4) RUN(8)
+  }
+  // the same ceiling for the other FP64 instructions (warp-instructions per clock per SM; a "flop" column would
+  // count DADD / DMUL as one): is a DFMA dearer than a DADD or DMUL on this pipe?
+  const char * names[] = {"DFMA", "DADD", "DMUL", "DMUL/DADD"};
+  for (int w : {4, 16})
+  {
+    double ipc[4][3];
+    run<1, 0>(w, p.multiProcessorCount, d_out, &ipc[0][0], clock_khz); run<2, 0>(w, p.multiProcessorCount, d_out, &ipc[0][1], clock_khz); run<4, 0>(w, p.multiProcessorCount, d_out, &ipc[0][2], clock_khz);
+    run<1, 1>(w, p.multiProcessorCount, d_out, &ipc[1][0], clock_khz); run<2, 1>(w, p.multiProcessorCount, d_out, &ipc[1][1], clock_khz); run<4, 1>(w, p.multiProcessorCount, d_out, &ipc[1][2], clock_khz);
+    run<1, 2>(w, p.multiProcessorCount, d_out, &ipc[2][0], clock_khz); run<2, 2>(w, p.multiProcessorCount, d_out, &ipc[2][1], clock_khz); run<4, 2>(w, p.multiProcessorCount, d_out, &ipc[2][2], clock_khz);
+    run<1, 3>(w, p.multiProcessorCount, d_out, &ipc[3][0], clock_khz); run<2, 3>(w, p.multiProcessorCount, d_out, &ipc[3][1], clock_khz); run<4, 3>(w, p.multiProcessorCount, d_out, &ipc[3][2], clock_khz);
+    for (int o = 0; o < 4; ++o)
+      printf("op %-10s warps %2d  inst/clk/SM at ILP 1/2/4: %.4f %.4f %.4f\n", names[o], w, ipc[o][0], ipc[o][1], ipc[o][2]);
   }
   printf("fp64_peak_tflops %.3f (nominal clock; DFMA = 2 flop)\n", best);
   return 0;
