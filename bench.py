@@ -15,8 +15,9 @@ Printed JSON (rank 0, one line): the contract keys, plus
                  (3 face-flux reads + 3 writes, as the reference moves them) / CUDA-event time
   cpu_baseline - the UNMODIFIED reference (oracle/_ref/ref_harness, OpenMP) timed on this box's
                  host cores on a bounded 64^3 sample of the same case
-  e2e          - the same step driven through doma_b200_sweep_from_host with HOST buffers
-                 (q: pinned host -> device, phi_cur: device -> host, every sweep)
+  e2e          - the same step driven through the host-buffer calls (doma_b200_stage_q_from_host /
+                 doma_b200_sweep_from_host_async / doma_b200_host_wait): q pinned host -> device and
+                 phi_cur device -> host for every sweep, copies overlapped with the neighbouring kernels
 --impl reference times the reference itself (rank 0 only) on the bounded sample, same metric.
 """
 import argparse
@@ -265,19 +266,31 @@ def main():
     e2e = None
     if not a.no_e2e:
         qh = torch.empty((G, N), dtype=torch.float64).pin_memory()
-        ph = torch.empty((N,), dtype=torch.float64).pin_memory()
+        ph = torch.empty((G, N), dtype=torch.float64).pin_memory()
         qh.copy_(torch.rand((G, N), dtype=torch.float64, generator=torch.Generator().manual_seed(1)))
         qn, pn = qh.numpy(), ph.numpy()
 
+        staged = [False]
+
         def e2e_step():
-            # the same Gauss-Seidel pass as step(), with the sweep driven through the host-buffer call:
-            # q goes pinned host -> device, phi_cur comes back device -> host, every sweep
+            # the same Gauss-Seidel pass as step(), with every sweep driven through the host-buffer calls: q of the
+            # group goes pinned host -> device, the (all-reduced) phi_cur comes back device -> host.  The calls are the
+            # asynchronous pair, so the copies of one group run under the kernels of its neighbours; the step ends
+            # with host_wait(), i.e. every byte has landed inside the timed region.
+            # (the source of the next sweep - of the next step's first group after the last one - is staged as soon
+            # as the current sweep is enqueued: every step still uploads its G sources once)
+            if not staged[0]:
+                ctx.stage_q_from_host(qn[0])
             for g in range(G):
                 ctx.update_mg_source(g, 0.0)
-                ctx.sweep_from_host(g, qn[g], pn)   # all-reduces phi_cur before the D2H when sharded
+                ctx.sweep_from_host_async(g, None, pn[g])
+                ctx.stage_q_from_host(qn[(g + 1) % G])
+                staged[0] = True
                 ctx.scatter_residual(g)
                 ctx.update_scatter_source(g)
-            return ctx.mg_residual() + float(pn[0])
+            r = ctx.mg_residual()
+            ctx.host_wait()
+            return r + float(pn[G - 1][0])
 
         for _ in range(2):
             e2e_step()
@@ -294,7 +307,7 @@ def main():
             de = float(t.item())
         e2e = {"value": updates_per_step * a.steps / de, "unit": UNIT, "h2d_bytes_per_step": 8 * N * G,
                "d2h_bytes_per_step": 8 * N * G, "ms_per_step": de / a.steps * 1e3,
-               "api": "doma_b200_sweep_from_host (C ABI, host buffers) per group + the step's source/residual calls"}
+               "api": "doma_b200_stage_q_from_host + doma_b200_sweep_from_host_async + doma_b200_host_wait (C ABI, pinned host buffers, copies overlapped with the neighbouring groups' kernels) per group + the step's source/residual calls"}
 
     if rank != 0:
         if world > 1:

@@ -200,6 +200,9 @@ class Library:
         "last_sweep_ms": [C.c_void_p, C.POINTER(C.c_float)],
         "set_threads": [C.c_void_p, C.c_int32],
         "sweep_from_host": [C.c_void_p, C.c_int32, _pd, _pd],
+        "stage_q_from_host": [C.c_void_p, _pd],
+        "sweep_from_host_async": [C.c_void_p, C.c_int32, _pd, _pd],
+        "host_wait": [C.c_void_p],
         "comm_unique_id": [C.c_char_p, C.c_int32],
         "comm_init": [C.c_void_p, C.c_int32, C.c_int32, C.c_char_p, C.c_int32],
         "allreduce_phi_cur": [C.c_void_p],
@@ -295,6 +298,19 @@ class Context:
         """Host-buffer form of sweep(g): H2D of q, sweep, D2H of phi_cur, all inside the call."""
         assert q_host.dtype == np.float64 and phi_out.dtype == np.float64
         self._call("sweep_from_host", int(g), q_host.ctypes.data_as(_pd), phi_out.ctypes.data_as(_pd))
+
+    def stage_q_from_host(self, q_host: np.ndarray):
+        """Start the H2D copy of the next sweep's source (pinned memory) on the copy stream."""
+        assert q_host.dtype == np.float64 and q_host.flags.c_contiguous
+        self._call("stage_q_from_host", q_host.ctypes.data_as(_pd))
+
+    def sweep_from_host_async(self, g: int, q_host: Optional[np.ndarray], phi_out: np.ndarray):
+        """Enqueue H2D of q (or use the staged one when q_host is None), sweep, D2H of phi_cur; see host_wait."""
+        assert phi_out.dtype == np.float64 and phi_out.flags.c_contiguous
+        qp = q_host.ctypes.data_as(_pd) if q_host is not None else C.cast(None, _pd)
+        self._call("sweep_from_host_async", int(g), qp, phi_out.ctypes.data_as(_pd))
+
+    def host_wait(self): self._call("host_wait")
 
     # reductions ----------------------------------------------------------------------------------
     def source_iteration(self, g: int, tol: float, max_it: int):

@@ -284,7 +284,8 @@ create_impl(doma_b200_ctx * c, const doma_b200_problem * p)
   }
   DOMA_CUDA(c, cudaMalloc(&c->red_partial, sizeof(double) * 2 * 1184));
   DOMA_CUDA(c, cudaMalloc(&c->red_out, sizeof(double) * 2));
-  DOMA_CUDA(c, cudaMallocHost(&c->h_red, sizeof(double) * 2));
+  DOMA_CUDA(c, cudaHostAlloc(&c->h_red, sizeof(double) * 2, cudaHostAllocMapped));
+  DOMA_CUDA(c, cudaHostGetDevicePointer(&c->h_red_dev, c->h_red, 0));
   return 0;
 }
 
@@ -375,6 +376,13 @@ doma_b200_destroy(doma_b200_ctx * c)
   for (void * p : ptrs)
     if (p)
       cudaFree(p);
+  if (c->async_ready)
+  {
+    cudaStreamSynchronize(c->copy_in), cudaStreamSynchronize(c->copy_out);
+    cudaFree(c->q_stage), cudaFree(c->phi_snap);
+    cudaEventDestroy(c->ev_q_staged), cudaEventDestroy(c->ev_q_consumed), cudaEventDestroy(c->ev_snap), cudaEventDestroy(c->ev_copied);
+    cudaStreamDestroy(c->copy_in), cudaStreamDestroy(c->copy_out);
+  }
   if (c->h_red)
     cudaFreeHost(c->h_red);
   if (c->ev0)
@@ -399,6 +407,11 @@ int
 doma_b200_set_stream(doma_b200_ctx * c, void * s)
 {
   DOMA_CUDA(c, cudaStreamSynchronize(c->stream));
+  if (c->async_ready)
+  {
+    DOMA_CUDA(c, cudaStreamSynchronize(c->copy_in));
+    DOMA_CUDA(c, cudaStreamSynchronize(c->copy_out));
+  }
   if (s)
   {
     if (c->own_stream)
@@ -418,6 +431,12 @@ int
 doma_b200_synchronize(doma_b200_ctx * c)
 {
   DOMA_CUDA(c, cudaStreamSynchronize(c->stream));
+  if (c->async_ready)
+  {
+    DOMA_CUDA(c, cudaStreamSynchronize(c->copy_in));
+    DOMA_CUDA(c, cudaStreamSynchronize(c->copy_out));
+    c->copy_pending = false;
+  }
   return 0;
 }
 
@@ -485,6 +504,103 @@ doma_b200_sweep_from_host(doma_b200_ctx * c, int32_t g, const double * q_host, d
     return rc;
   DOMA_CUDA(c, cudaMemcpyAsync(phi_cur_out, c->phi_cur, sizeof(double) * c->N, cudaMemcpyDeviceToHost, c->stream));
   DOMA_CUDA(c, cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+// ---- asynchronous host-buffer sweeps: the copies of one group overlap the kernels of its neighbours ----
+// copy_in:  H2D q_host -> q_stage                      (may run while the previous sweep is still executing)
+// stream:   q_stage -> q, phi_cur = 0, sweep, all-reduce, phi_cur -> phi_snap
+// copy_out: D2H phi_snap -> phi_cur_out                (runs under the next group's source build and sweep)
+namespace
+{
+int
+async_setup(doma_b200_ctx * c)
+{
+  if (c->async_ready)
+    return 0;
+  DOMA_CUDA(c, cudaMalloc(&c->q_stage, sizeof(double) * c->N));
+  DOMA_CUDA(c, cudaMalloc(&c->phi_snap, sizeof(double) * c->N));
+  c->device_bytes += 2 * (int64_t)sizeof(double) * c->N;
+  DOMA_CUDA(c, cudaStreamCreateWithFlags(&c->copy_in, cudaStreamNonBlocking));
+  DOMA_CUDA(c, cudaStreamCreateWithFlags(&c->copy_out, cudaStreamNonBlocking));
+  DOMA_CUDA(c, cudaEventCreateWithFlags(&c->ev_q_staged, cudaEventDisableTiming));
+  DOMA_CUDA(c, cudaEventCreateWithFlags(&c->ev_q_consumed, cudaEventDisableTiming));
+  DOMA_CUDA(c, cudaEventCreateWithFlags(&c->ev_snap, cudaEventDisableTiming));
+  DOMA_CUDA(c, cudaEventCreateWithFlags(&c->ev_copied, cudaEventDisableTiming));
+  // "free" state: nothing staged, nothing pending
+  DOMA_CUDA(c, cudaEventRecord(c->ev_q_consumed, c->stream));
+  DOMA_CUDA(c, cudaEventRecord(c->ev_copied, c->copy_out));
+  c->async_ready = true;
+  return 0;
+}
+} // namespace
+
+int
+doma_b200_stage_q_from_host(doma_b200_ctx * c, const double * q_host)
+{
+  ENTER(c);
+  if (!q_host)
+  {
+    snprintf(c->err, DOMA_MAX_ERR, "stage_q_from_host: null host pointer");
+    return 1;
+  }
+  if (c->q_is_staged)
+  {
+    snprintf(c->err, DOMA_MAX_ERR, "stage_q_from_host: a staged source is still waiting for its sweep");
+    return 1;
+  }
+  int rc = async_setup(c);
+  if (rc)
+    return rc;
+  DOMA_CUDA(c, cudaStreamWaitEvent(c->copy_in, c->ev_q_consumed, 0)); // the previous staged source has left q_stage
+  DOMA_CUDA(c, cudaMemcpyAsync(c->q_stage, q_host, sizeof(double) * c->N, cudaMemcpyHostToDevice, c->copy_in));
+  DOMA_CUDA(c, cudaEventRecord(c->ev_q_staged, c->copy_in));
+  c->q_is_staged = true;
+  return 0;
+}
+
+int
+doma_b200_sweep_from_host_async(doma_b200_ctx * c, int32_t g, const double * q_host, double * phi_cur_out)
+{
+  ENTER(c);
+  CHECK_GROUP(c, g);
+  if (!phi_cur_out || (!q_host && !c->q_is_staged))
+  {
+    snprintf(c->err, DOMA_MAX_ERR, "sweep_from_host_async: %s", !phi_cur_out ? "null output pointer" : "no source: pass q_host or stage one first");
+    return 1;
+  }
+  int rc = 0;
+  if (q_host && (rc = doma_b200_stage_q_from_host(c, q_host)))
+    return rc;
+  DOMA_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_q_staged, 0));
+  if ((rc = doma_launch_stage_in(c)))
+    return rc;
+  DOMA_CUDA(c, cudaEventRecord(c->ev_q_consumed, c->stream));
+  c->q_is_staged = false;
+  if ((rc = doma_launch_sweep(c, g)))
+    return rc;
+  if (c->nccl_comm && (rc = doma_b200_allreduce_phi_cur(c)))
+    return rc;
+  DOMA_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_copied, 0)); // the previous result has left phi_snap
+  if ((rc = doma_launch_snapshot_phi_cur(c)))
+    return rc;
+  DOMA_CUDA(c, cudaEventRecord(c->ev_snap, c->stream));
+  DOMA_CUDA(c, cudaStreamWaitEvent(c->copy_out, c->ev_snap, 0));
+  DOMA_CUDA(c, cudaMemcpyAsync(phi_cur_out, c->phi_snap, sizeof(double) * c->N, cudaMemcpyDeviceToHost, c->copy_out));
+  DOMA_CUDA(c, cudaEventRecord(c->ev_copied, c->copy_out));
+  c->copy_pending = true;
+  return 0;
+}
+
+int
+doma_b200_host_wait(doma_b200_ctx * c)
+{
+  ENTER(c);
+  if (c->copy_pending)
+  {
+    DOMA_CUDA(c, cudaEventSynchronize(c->ev_copied));
+    c->copy_pending = false;
+  }
   return 0;
 }
 

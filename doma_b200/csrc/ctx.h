@@ -72,12 +72,20 @@ struct doma_b200_ctx
   // reductions
   double * red_partial; // [2 * RED_BLOCKS]
   double * red_out;     // [2] device
-  double * h_red;       // [2] pinned host
+  double * h_red;       // [2] pinned, mapped host memory
+  double * h_red_dev;   // the device-side address of h_red (final_reduce_kernel stores into it)
 
   // timing / accounting
   cudaEvent_t ev0, ev1;
   bool have_sweep_time;
   int64_t launches;
+
+  // asynchronous host-buffer sweeps (api.cu, doma_b200_sweep_from_host_async): staging buffers, copy streams
+  // and the events that order them against the context's stream; created on first use
+  double *q_stage, *phi_snap;
+  cudaStream_t copy_in, copy_out;
+  cudaEvent_t ev_q_staged, ev_q_consumed, ev_snap, ev_copied;
+  bool async_ready, q_is_staged, copy_pending;
 
   // NCCL (resolved with dlopen at comm_init; see api.cu)
   void * nccl_comm;
@@ -105,6 +113,8 @@ int doma_launch_step_dnps(doma_b200_ctx * c);
 int doma_launch_update_mg_source(doma_b200_ctx * c, int g, double t);
 int doma_launch_update_mg_source_eigen(doma_b200_ctx * c, int g, double k);
 int doma_launch_update_scatter_source(doma_b200_ctx * c, int g);
+int doma_launch_stage_in(doma_b200_ctx * c);          // q = q_stage, phi_cur = 0
+int doma_launch_snapshot_phi_cur(doma_b200_ctx * c);  // phi_snap = phi_cur
 int doma_launch_scatter_residual(doma_b200_ctx * c, int g); // leaves (diff, total) in h_red after sync
 int doma_launch_scatter_residual_update(doma_b200_ctx * c, int g); // fused pair, leaves (diff, total) in h_red
 int doma_launch_mg_residual(doma_b200_ctx * c);

@@ -54,6 +54,27 @@ fill_kernel(double * __restrict__ p, int64_t n, double v)
     p[i] = v;
 }
 
+// device-to-device moves of the asynchronous host-buffer sweeps, as kernels: a cudaMemcpyAsync D2D may be put on the
+// copy engine that is busy with the neighbouring group's PCIe transfer and then waits 2.5 ms for it (measured)
+__global__ void
+stage_in_kernel(double * __restrict__ q, const double * __restrict__ q_stage, double * __restrict__ phi_cur, int64_t n)
+{
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n)
+  {
+    q[i] = q_stage[i];
+    phi_cur[i] = 0.0;
+  }
+}
+
+__global__ void
+copy_kernel(double * __restrict__ dst, const double * __restrict__ src, int64_t n)
+{
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n)
+    dst[i] = src[i];
+}
+
 // stepDNPs (3D:236-260)
 __global__ void
 step_dnps_kernel(int64_t N, int G, int D, double dt, const int32_t * __restrict__ mat, const int32_t * __restrict__ n_delayed,
@@ -333,7 +354,7 @@ k_sums_kernel(int64_t N, int G, double k, Geo geo, const int32_t * __restrict__ 
 }
 
 __global__ void
-final_reduce_kernel(const double * __restrict__ partial, double * __restrict__ out)
+final_reduce_kernel(const double * __restrict__ partial, double * __restrict__ out, double * __restrict__ out_host)
 {
   // 2 warps: warp 0 sums the first RED_BLOCKS partials, warp 1 the second; lane-strided then a
   // fixed shuffle tree -> deterministic
@@ -344,16 +365,22 @@ final_reduce_kernel(const double * __restrict__ partial, double * __restrict__ o
   for (int o = 16; o > 0; o >>= 1)
     a += __shfl_down_sync(0xffffffffu, a, o);
   if (lane == 0)
+  {
     out[w] = a;
+    // the pair also lands in pinned host memory straight from the kernel (zero-copy store): a 16-byte
+    // cudaMemcpyAsync would queue on the D2H copy engine behind a 134 MB result transfer of an
+    // asynchronous host-buffer sweep and cost the stream 2.5 ms (measured, scripts/e2e_probe.py)
+    out_host[w] = a;
+    __threadfence_system();
+  }
 }
 
 int
 finish_reduce(doma_b200_ctx * c)
 {
-  final_reduce_kernel<<<1, 64, 0, c->stream>>>(c->red_partial, c->red_out);
+  final_reduce_kernel<<<1, 64, 0, c->stream>>>(c->red_partial, c->red_out, c->h_red_dev);
   c->launches += 2;
   DOMA_CUDA(c, cudaGetLastError());
-  DOMA_CUDA(c, cudaMemcpyAsync(c->h_red, c->red_out, 2 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
   DOMA_CUDA(c, cudaStreamSynchronize(c->stream));
   return 0;
 }
@@ -369,6 +396,24 @@ doma_launch_reset_state(doma_b200_ctx * c, double phi_init)
   DOMA_CUDA(c, cudaMemsetAsync(c->phi_prev, 0, sizeof(double) * GN, c->stream));
   DOMA_CUDA(c, cudaMemsetAsync(c->q, 0, sizeof(double) * c->N, c->stream));
   DOMA_CUDA(c, cudaMemsetAsync(c->phi_cur, 0, sizeof(double) * c->N, c->stream));
+  return 0;
+}
+
+int
+doma_launch_stage_in(doma_b200_ctx * c)
+{
+  stage_in_kernel<<<ew_blocks(c->N), EW_THREADS, 0, c->stream>>>(c->q, c->q_stage, c->phi_cur, c->N);
+  c->launches += 1;
+  DOMA_CUDA(c, cudaGetLastError());
+  return 0;
+}
+
+int
+doma_launch_snapshot_phi_cur(doma_b200_ctx * c)
+{
+  copy_kernel<<<ew_blocks(c->N), EW_THREADS, 0, c->stream>>>(c->phi_snap, c->phi_cur, c->N);
+  c->launches += 1;
+  DOMA_CUDA(c, cudaGetLastError());
   return 0;
 }
 

@@ -121,6 +121,18 @@ int doma_b200_sweep(doma_b200_ctx * ctx, int32_t g);
  * cell order) to the device, zeroes phi_cur, sweeps, copies phi_cur back into phi_cur_out. Synchronous. */
 int doma_b200_sweep_from_host(doma_b200_ctx * ctx, int32_t g, const double * q_host, double * phi_cur_out);
 
+/* Asynchronous form of the host-buffer sweep, for callers that pipeline groups: the same work as
+ * doma_b200_sweep_from_host, enqueued and returned from at once.  The host-to-device copy of q runs on a copy
+ * stream (doma_b200_stage_q_from_host may start it early, while the previous sweep is still running; then pass
+ * q_host = NULL here), the device-to-host copy of phi_cur on another one, under whatever the caller enqueues next.
+ * q_host must stay valid and unchanged, and phi_cur_out is only complete, once doma_b200_host_wait (or
+ * doma_b200_synchronize) has returned.
+ * One staged source and one pending result at a time per context (a second stage before its sweep is an error;
+ * a second sweep waits for the previous result to leave the staging buffer). */
+int doma_b200_stage_q_from_host(doma_b200_ctx * ctx, const double * q_host);
+int doma_b200_sweep_from_host_async(doma_b200_ctx * ctx, int32_t g, const double * q_host, double * phi_cur_out);
+int doma_b200_host_wait(doma_b200_ctx * ctx);
+
 /* sourceIteration(g) (3D:458-497) as ONE call (the fused inner iteration of SURVEY.md 8f-1):
  *   do { sweep(g); all-reduce phi_cur over ranks; residual = computeScatteringResidual(g); updateScatteringSource(g); it++ }
  *   while (it < max_it && tol < residual);

@@ -105,6 +105,42 @@ def test_sweep_from_host_equals_resident(cuda_lib):
     assert relmax(b, a) <= 1e-13
 
 
+@pytest.mark.gpu
+def test_async_host_sweep_equals_sync(cuda_lib):
+    """stage_q_from_host / sweep_from_host_async / host_wait give the bytes sweep_from_host gives, also when
+    the next source is staged while a sweep is in flight and results are collected late."""
+    prob = random_problem((20, 9, 7), G=3, npol=2, nazi=2, seed=11)
+    rng = np.random.default_rng(5)
+    qs = [rng.uniform(0, 1, prob.n_cells) for _ in range(3)]
+    ref = []
+    ctx = abi.Context(prob, cuda_lib)
+    ctx.reset_state(0.0)
+    for g in range(3):
+        out = np.zeros(prob.n_cells)
+        ctx.sweep_from_host(g, qs[g], out)
+        ref.append(out)
+    ctx2 = abi.Context(prob, cuda_lib)
+    ctx2.reset_state(0.0)
+    outs = [np.zeros(prob.n_cells) for _ in range(3)]
+    ctx2.stage_q_from_host(qs[0])
+    for g in range(3):
+        ctx2.sweep_from_host_async(g, None, outs[g])
+        if g + 1 < 3:
+            ctx2.stage_q_from_host(qs[g + 1])
+        ctx2.scatter_residual(g)           # a synchronising call in between, as in the solver loop
+    ctx2.host_wait()
+    for g in range(3):
+        assert relmax(outs[g], ref[g]) <= 1e-13   # RED order differs between launches, values do not
+    with pytest.raises(abi.DomaError):
+        ctx2.stage_q_from_host(qs[0]); ctx2.stage_q_from_host(qs[1])
+    ctx2.sweep_from_host_async(0, None, outs[0]); ctx2.synchronize()
+    out = np.zeros(prob.n_cells)
+    ctx2.sweep_from_host_async(1, qs[1], out)      # unstaged form
+    ctx2.host_wait()
+    assert relmax(out, ref[1]) <= 1e-13
+
+
+
 def test_elementwise_kernels_bit_identical(cuda_lib, oracle_lib):
     """Source build / update / DNP step: same per-cell arithmetic, no FMA -> identical bits."""
     # G = 9 takes the kernels' run-time group loop (groups 1..8 are compile-time specialisations)
