@@ -244,22 +244,6 @@ create_impl(doma_b200_ctx * c, const doma_b200_problem * p)
   UP(step_t_remove, p->step_t_remove, M);
   UP(step_src, p->step_src, M * G);
 #undef UP
-  for (size_t g = 0; g < 32; ++g)
-    c->src_need[g] = 0xffffffffu;
-  if (G <= 32)
-    for (size_t g = 0; g < G; ++g)
-    {
-      uint32_t need = 0;
-      for (size_t m = 0; m < M; ++m)
-        for (size_t gp = 0; gp < G; ++gp)
-        {
-          const bool scat = gp != g && p->sigma_s[(m * G + g) * G + gp] != 0.0;
-          const bool fiss = p->chi_p && p->nu_sigma_f && (p->mat_flags[m] & DOMA_MAT_HAS_CHI_P) && p->chi_p[m * G + g] != 0.0 && p->nu_sigma_f[m * G + gp] != 0.0;
-          if (scat || fiss)
-            need |= 1u << gp;
-        }
-      c->src_need[g] = need;
-    }
   if ((rc = alloc_zero(c, &c->sig_cell, (size_t)c->N)))
     return rc;
   c->sig_cell_group = -1;

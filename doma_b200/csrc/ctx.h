@@ -69,10 +69,6 @@ struct doma_b200_ctx
   int epoch;
   int64_t face_bytes, device_bytes;
 
-  // bit g' of src_need[g]: some material scatters or fissions from group g' into group g, i.e. the source
-  // build of g has to read phi_tot[g'] (all ones when G > 32)
-  uint32_t src_need[32];
-
   // reductions
   double * red_partial; // [2 * RED_BLOCKS]
   double * red_out;     // [2] device

@@ -103,7 +103,7 @@ step_dnps_kernel(int64_t N, int G, int D, double dt, const int32_t * __restrict_
 // loads of phi_tot are issued up front instead of one per iteration behind an IEEE division.
 template <int GT>
 __global__ void
-mg_source_kernel(int64_t N, int G, int D, int g, double t, double f, int transient, double dt, uint32_t need,
+mg_source_kernel(int64_t N, int G, int D, int g, double t, double f, int transient, double dt,
                  const int32_t * __restrict__ mat, const int32_t * __restrict__ mat_flags,
                  const int32_t * __restrict__ n_delayed, const int32_t * __restrict__ step_type,
                  const double * __restrict__ step_t_insert, const double * __restrict__ step_t_remove,
@@ -125,7 +125,7 @@ mg_source_kernel(int64_t N, int G, int D, int g, double t, double f, int transie
   {
 #pragma unroll
     for (int gp = 0; gp < GT; ++gp)
-      ph[gp] = (need >> gp) & 1u ? phi_tot[gp * N + i] : 0.0; // groups no material couples into g are not read
+      ph[gp] = phi_tot[gp * N + i];
   }
   double q = (mat_flags[m] & DOMA_MAT_HAS_SRC) ? f * src[m * G + g] / M_PI : 0.0;
   if (transient && step_type[m] != DOMA_STEP_NONE)
@@ -175,7 +175,7 @@ mg_source_kernel(int64_t N, int G, int D, int g, double t, double f, int transie
 // updateMultigroupSourceEigen(g) (3D:404-430): "+=" onto the stale q
 template <int GT>
 __global__ void
-mg_source_eigen_kernel(int64_t N, int G, int g, double k, double f, uint32_t need, const int32_t * __restrict__ mat,
+mg_source_eigen_kernel(int64_t N, int G, int g, double k, double f, const int32_t * __restrict__ mat,
                        const int32_t * __restrict__ mat_flags, const double * __restrict__ sigma_s,
                        const double * __restrict__ chi_p, const double * __restrict__ nu_sigma_f,
                        double * __restrict__ phi_tot, double * __restrict__ phi_prev, double * __restrict__ q_io,
@@ -192,7 +192,7 @@ mg_source_eigen_kernel(int64_t N, int G, int g, double k, double f, uint32_t nee
   {
 #pragma unroll
     for (int gp = 0; gp < GT; ++gp)
-      ph[gp] = (need >> gp) & 1u ? phi_tot[gp * N + i] : 0.0;
+      ph[gp] = phi_tot[gp * N + i];
   }
   double q = q_io[i];
 #pragma unroll
@@ -468,7 +468,7 @@ doma_launch_update_mg_source(doma_b200_ctx * c, int g, double t)
   const int transient = c->mode == DOMA_MODE_TRANSIENT;
 #define MGS(GT)                                                                                                          \
   mg_source_kernel<GT><<<ew_blocks(c->N), EW_THREADS, 0, c->stream>>>(                                                   \
-      c->N, c->G, c->D, g, t, f, transient, c->dt, c->src_need[g & 31], c->mat, c->mat_flags, c->n_delayed, c->step_type, c->step_t_insert, \
+      c->N, c->G, c->D, g, t, f, transient, c->dt, c->mat, c->mat_flags, c->n_delayed, c->step_type, c->step_t_insert, \
       c->step_t_remove, c->step_src, c->src, c->sigma_s, c->chi_p, c->nu_sigma_f, c->beta, c->chi_d, c->lambda,        \
       c->inv_v, c->dnp_cur, c->phi_last, c->phi_tot, c->phi_prev, c->q, c->phi_cur)
   switch (c->G)
@@ -494,7 +494,7 @@ doma_launch_update_mg_source_eigen(doma_b200_ctx * c, int g, double k)
 {
   const double f = c->dims == 3 ? 0.25 : 0.5;
 #define MGE(GT)                                                                                                    \
-  mg_source_eigen_kernel<GT><<<ew_blocks(c->N), EW_THREADS, 0, c->stream>>>(c->N, c->G, g, k, f, c->src_need[g & 31], c->mat, c->mat_flags, \
+  mg_source_eigen_kernel<GT><<<ew_blocks(c->N), EW_THREADS, 0, c->stream>>>(c->N, c->G, g, k, f, c->mat, c->mat_flags, \
                                                                             c->sigma_s, c->chi_p, c->nu_sigma_f,     \
                                                                             c->phi_tot, c->phi_prev, c->q, c->phi_cur)
   switch (c->G)
