@@ -14,7 +14,7 @@ Printed JSON (rank 0, one line): the contract keys, plus
   roofline     - the sweep kernel against the HBM roofline: 48 algorithmic bytes per update
                  (3 face-flux reads + 3 writes, as the reference moves them) / CUDA-event time
   cpu_baseline - the UNMODIFIED reference (oracle/_ref/ref_harness, OpenMP) timed on this box's
-                 host cores on a bounded 64^3 sample of the same case
+                 host cores on a bounded sample of the same case (4 sweeps of group 0 at 128^3)
   e2e          - the same step driven through the host-buffer calls (doma_b200_stage_q_from_host /
                  doma_b200_sweep_from_host_async / doma_b200_host_wait): q pinned host -> device and
                  phi_cur device -> host for every sweep, copies overlapped with the neighbouring kernels
@@ -84,7 +84,7 @@ class ClockSampler:
                 "samples": len(sm), "reasons": reasons}
 
 
-def run_reference_sample(n, G, steps, warmup, threads, mode="B"):
+def run_reference_sample(n, G, steps, warmup, threads, mode="B", sweeps=1):
     """Times the unmodified reference on a bounded sample; returns (updates/s, seconds per step, description)."""
     from doma_b200.synthetic import synthetic_xml
 
@@ -94,7 +94,7 @@ def run_reference_sample(n, G, steps, warmup, threads, mode="B"):
     tmp = tempfile.mkdtemp(prefix="doma_ref_")
     xml = os.path.join(tmp, "sample.xml")
     with open(xml, "w") as f:
-        f.write(synthetic_xml(n, G=G, mode=mode, sweeps=1))
+        f.write(synthetic_xml(n, G=G, mode=mode, sweeps=sweeps))
     env = dict(os.environ, OMP_NUM_THREADS=str(threads), OMP_PROC_BIND="false")
     times = []
     for i in range(warmup + steps):
@@ -104,9 +104,9 @@ def run_reference_sample(n, G, steps, warmup, threads, mode="B"):
         sec = float(r.stdout.rsplit("solve_seconds=", 1)[1].split()[0])
         if i >= warmup:
             times.append(sec)
-    upd = float(n) ** 3 * 512 * (G if mode == "B" else 1)
+    upd = float(n) ** 3 * 512 * (G if mode == "B" else sweeps)
     sec = sum(times) / len(times)
-    what = f"one sweep of each of the {G} groups (Mode B)" if mode == "B" else "one sweep of group 0 (Mode A)"
+    what = f"one sweep of each of the {G} groups (Mode B)" if mode == "B" else f"{sweeps} sweep(s) of group 0 (Mode A)"
     return upd / sec, sec, (f"unmodified reference (ref_harness), synthetic {n}^3 cells x 512 ordinates, {what}, "
                             f"OpenMP {threads} threads, solve time only, mean of {steps} run(s) after {warmup} warm-up")
 
@@ -131,6 +131,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--tile", default="", help="TYxTZ override of the KBA tile, e.g. 4x8")
     ap.add_argument("--ref-n", type=int, default=64, help="cells per axis of the bounded CPU sample")
+    ap.add_argument("--cpu-n", type=int, default=128, help="cells per axis of the cpu_baseline sample (4 sweeps of group 0)")
     ap.add_argument("--emulate-world", type=int, default=0,
                     help="tuning aid, 1 GPU only: sweep rank 0's ordinate shard of a W-rank run (no all-reduce); "
                          "the line is marked 'emulated_world' and is not a bench value")
@@ -332,7 +333,8 @@ def main():
     cpu = None
     if not a.no_cpu_baseline and world == 1:
         T = host_threads()
-        v, sec, desc = run_reference_sample(a.ref_n, G, 1, 1, T, mode="A")
+        # bounded sample: 4 sweeps of group 0 at 128^3 = 4.3e9 updates, 10-15 s of work on 16 host threads
+        v, sec, desc = run_reference_sample(a.cpu_n, G, 1, 0, T, mode="A", sweeps=4)
         if v is not None:
             cpu = {"value": v, "unit": UNIT, "cores": T, "kind": "reference", "sample": desc}
         else:
