@@ -147,17 +147,30 @@ doma_build_units(doma_b200_ctx * c, int V)
   // resident warps are 16 per SM (4 CTAs x 4 warps); the measured optimum sits at 1.0-1.8 tasks in flight per
   // resident warp (2 units: 8x4x4 0.70 -> 7.53 ms, 8x4x2 1.00 -> 7.02 ms, 8x2x2 1.55 -> 7.61 ms), hence 15 not 16
   const double want = 15.0 * c->n_sms;
-  int pick = n_cand - 1;
+  // When no tile saturates the GPU (the shipped assembly and 2D cases) the sweep is a chain of task latencies,
+  // and the tile that minimises  hyperplanes x L + tasks x L / resident warps  wins, with the measured single-warp
+  // task latency L = cells x 0.195 us + 3.4 us (profiles/r01_task_latency.txt).  Measured: the 2D transient case
+  // 8x1 422 us, 8x2 299 us, 8x4 256 us per sweep (profiles/r01_small_case_tiles.txt).
+  int pick = -1, best = 0;
+  double best_cost = 0.0;
   for (int i = 0; i < n_cand; ++i)
   {
     const double ntx = (c->nx + 7) / 8, nty = (c->ny + cand[i][0] - 1) / cand[i][0], ntz = (c->nz + cand[i][1] - 1) / cand[i][1];
-    const double in_flight = (double)(c->n_units > 0 ? c->n_units : 1) * ntx * nty * ntz / (ntx + nty + ntz - 2.0);
+    const double units = c->n_units > 0 ? c->n_units : 1;
+    const double planes = ntx + nty + ntz - 2.0;
+    const double in_flight = units * ntx * nty * ntz / planes;
     if (in_flight >= want)
     {
       pick = i;
       break;
     }
+    const double L = 8.0 * cand[i][0] * cand[i][1] * 0.195 + 3.4;
+    const double cost = planes * L + units * ntx * nty * ntz * L / (16.0 * c->n_sms);
+    if (i == 0 || cost < best_cost)
+      best = i, best_cost = cost;
   }
+  if (pick < 0)
+    pick = best;
   rc = doma_sweep_setup_tiles(c, cand[pick][0], cand[pick][1]);
   c->tile_auto = true;
   return rc;
