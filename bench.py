@@ -36,6 +36,8 @@ METRIC = "sweep cell-angle-group updates/s"
 UNIT = "updates/s"
 BYTES_PER_UPDATE = 48.0   # 3 upwind face reads + 3 downwind face writes x 8 B
 FP64_OPS_PER_UPDATE = 118.0  # 13 divisions + 105 other FP64 operations as the reference writes them
+FP64_INST_PER_UPDATE = 55.7   # FP64-pipe instructions per update in the shipped SASS (368 DFMA + 264 DADD + 259 DMUL per 16 cells)
+FP64_WARP_INST_PER_CLK_SM = 2.0  # issue ceiling of the FP64 pipe: 64 lanes per SM (scripts/fp64_peak.cu measures 1.98 with DADD)
 
 
 def measured_peaks():
@@ -324,6 +326,11 @@ def main():
                 "launch_ms": mean_sweep_ms, "kernel_updates_per_s": upd_per_launch / (mean_sweep_ms * 1e-3),
                 "fp64_gflops_algorithmic": upd_per_launch * FP64_OPS_PER_UPDATE / (mean_sweep_ms * 1e-3) / 1e9,
                 "sweep_share_of_step": mean_sweep_ms * G * a.steps / (dt * 1e3)}
+    sm_mhz = (clocks or {}).get("sm_mhz") or 1965.0
+    roofline["fp64_pipe_frac"] = (roofline["kernel_updates_per_s"] / 32.0 * FP64_INST_PER_UPDATE /
+                                  torch.cuda.get_device_properties(local).multi_processor_count /
+                                  (FP64_WARP_INST_PER_CLK_SM * sm_mhz * 1e6))
+    roofline["fp64_pipe_note"] = "the binding roof (DESIGN.md 3.3): FP64-pipe warp-instructions issued / (2 per clk per SM x SM clock)"
     prof = os.path.join(ROOT, "profiles", "sweep_traffic.json")
     if os.path.exists(prof):
         try:
