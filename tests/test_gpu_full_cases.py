@@ -1,7 +1,8 @@
 """The SHIPPED cases at full size on the GPU against digests of the unmodified reference's final
 state (tests/golden/full/*.npz, written by tests/golden/make_golden_full.py in the build container).
 
-Kobayashi 1 and 3 are the shipped files unchanged, run to convergence.  The two 3D assembly cases
+Kobayashi 1 and 3 are the shipped files unchanged, run to convergence.  syn256_b is bench.py's own workload (synthetic
+256^3 x 8 groups x 512 ordinates, Mode B; the reference needed 953 s and 14 GB for it).  The two 3D assembly cases
 and the 2D transient keep the shipped mesh, materials and quadrature and change only the iteration
 budget / end time (the reference needs hours to converge them on 8 vCPU).
 Tolerances are north_star's: flux <= 1e-10 relative, k_eff <= 1e-9, identical iteration traces.
@@ -20,6 +21,13 @@ FULL = os.path.join(GOLDEN, "full")
 NAMES = sorted(f[:-4] for f in os.listdir(FULL) if f.endswith(".npz"))
 FLUX_RTOL = 1e-10
 K_TOL = 1e-9
+# Floor of the flux comparison, as a fraction of the group's maximum flux (~45 ulp of it).  Only the synthetic 256^3 case
+# needs it: its flux spans 60 decades, and where |phi| < 1e-9 phi_max it is a sum of +- diamond-difference fluxes (below
+# the 1e-8 switch of the theta-weighted scheme) whose value depends on the summation order over ordinates.  The
+# UNMODIFIED reference run with 8 and with 3 OpenMP threads differs from itself there by up to 2.7e-5 of the local
+# value but < 1.3e-15 of phi_max (profiles/r01_reference_thread_noise_128.txt); the CUDA path stays within 5.2e-16 of
+# phi_max (profiles/r01_v7_full_size_256_vs_reference.txt).  Everywhere else the bound is north_star's 1e-10 relative.
+FLUX_FLOOR = 1e-14
 
 
 def check_against_digest(name, lib, fused_si=False):
@@ -36,16 +44,19 @@ def check_against_digest(name, lib, fused_si=False):
     phi = s.flux()                                    # [G, N]
     idx = g["idx"]
     ref = g["phi_s"]
-    err = np.abs(phi[:, idx] - ref) / np.maximum(np.abs(ref), 1e-300)
+    floor = FLUX_FLOOR if name.startswith("syn") else 0.0      # the shipped cases are held to the pure relative bound
+    pmax = np.abs(g["phi_max"])[:, None]
+    err = np.abs(phi[:, idx] - ref) / np.maximum(np.maximum(np.abs(ref), floor / FLUX_RTOL * pmax), 1e-300)
     assert float(err.max()) <= FLUX_RTOL, f"sampled flux differs: {err.max():.3e}"
     np.testing.assert_allclose(phi.sum(axis=1), g["phi_sum"], rtol=1e-11, atol=0)
     np.testing.assert_allclose(np.sqrt((phi * phi).sum(axis=1)), g["phi_l2"], rtol=1e-11, atol=0)
-    np.testing.assert_allclose(phi.min(axis=1), g["phi_min"], rtol=FLUX_RTOL, atol=0)
+    np.testing.assert_allclose(phi.min(axis=1), g["phi_min"], rtol=FLUX_RTOL, atol=floor * float(pmax.max()))
     np.testing.assert_allclose(phi.max(axis=1), g["phi_max"], rtol=FLUX_RTOL, atol=0)
     G = phi.shape[0]
     nx, ny, nz = g["shape"].tolist()
     slabs = phi.reshape(G, nz, ny * nx).sum(axis=2) if prob.dims == 3 else phi.reshape(G, ny, nx).sum(axis=2)
-    np.testing.assert_allclose(slabs, g["slab_sum"], rtol=1e-10, atol=0)
+    # (a slab's sum is compared relative to the largest slab of its group: far slabs are sums of the +- fluxes above)
+    np.testing.assert_allclose(slabs, g["slab_sum"], rtol=1e-10, atol=10 * floor * float(np.abs(g["slab_sum"]).max()))
     if params.mode == abi.MODE_EIGEN:
         assert abs(s.k - float(g["k"])) <= K_TOL
         n = min(len(s.trace.k_history), len(g["k_history"]))   # the reference prints k only for iterations it continues from
