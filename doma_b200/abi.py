@@ -203,6 +203,10 @@ class Library:
         "stage_q_from_host": [C.c_void_p, _pd],
         "sweep_from_host_async": [C.c_void_p, C.c_int32, _pd, _pd],
         "host_wait": [C.c_void_p],
+        "dump_text": [C.c_void_p, C.c_char_p, C.c_int32, C.c_int32],
+        "dump_text_async": [C.c_void_p, C.c_char_p, C.c_int32, C.c_int32],
+        "dump_wait": [C.c_void_p],
+        "write_values_text": [_pd, C.c_int64, C.c_char_p, C.c_int32],
         "comm_unique_id": [C.c_char_p, C.c_int32],
         "comm_init": [C.c_void_p, C.c_int32, C.c_int32, C.c_char_p, C.c_int32],
         "allreduce_phi_cur": [C.c_void_p],
@@ -246,6 +250,15 @@ def load_library() -> Library:
     if _default_lib is None:
         _default_lib = Library(LIB_PATH, "doma_b200_")
     return _default_lib
+
+
+def write_values_text(values: np.ndarray, path: str, threads: int = 0, lib: Optional[Library] = None):
+    """One "%.6g" value per line, the reference's text format; pure host code of the product library."""
+    lib = lib or load_library()
+    v = np.ascontiguousarray(values, dtype=np.float64).reshape(-1)
+    rc = lib.fn["write_values_text"](v.ctypes.data_as(_pd), v.size, os.fsencode(path), int(threads))
+    if rc:
+        raise DomaError(f"write_values_text failed ({rc}): {lib.last_error(None)}")
 
 
 class Context:
@@ -311,6 +324,16 @@ class Context:
         self._call("sweep_from_host_async", int(g), qp, phi_out.ctypes.data_as(_pd))
 
     def host_wait(self): self._call("host_wait")
+
+    def dump_text(self, file_base: str, with_dnps: bool = False, threads: int = 0):
+        """<base>_g<g>_flux.txt (and <base>_d<d>_dnps.txt): the bytes BrickMesh::dumpToTextFile / dumpDNPsToTextFile write."""
+        self._call("dump_text", os.fsencode(file_base), int(bool(with_dnps)), int(threads))
+
+    def dump_text_async(self, file_base: str, with_dnps: bool = False, threads: int = 0):
+        """dump_text overlapped with the caller's next work (host snapshot now, files on a worker thread); see dump_wait."""
+        self._call("dump_text_async", os.fsencode(file_base), int(bool(with_dnps)), int(threads))
+
+    def dump_wait(self): self._call("dump_wait")
 
     # reductions ----------------------------------------------------------------------------------
     def source_iteration(self, g: int, tol: float, max_it: int):

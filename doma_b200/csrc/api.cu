@@ -7,6 +7,9 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <algorithm>
+#include <string>
+#include <thread>
 #include <vector>
 
 namespace
@@ -377,6 +380,7 @@ doma_b200_destroy(doma_b200_ctx * c)
   if (!c)
     return 0;
   cudaSetDevice(c->device);
+  doma_b200_dump_wait(c);
   if (c->stream)
     cudaStreamSynchronize(c->stream);
   if (c->nccl_comm && g_nccl.CommDestroy)
@@ -810,6 +814,189 @@ doma_b200_last_sweep_ms(doma_b200_ctx * c, float * out)
   DOMA_CUDA(c, cudaEventSynchronize(c->ev1));
   DOMA_CUDA(c, cudaEventElapsedTime(out, c->ev0, c->ev1));
   return 0;
+}
+
+// ---- text output (BrickMesh3D::dumpToTextFile / dumpDNPsToTextFile, src/BrickMesh3D.cpp:216-295; 2D: src/BrickMesh2D.cpp) ----
+// The reference writes one value per line with `stream << std::setprecision(6) << value << std::endl`, i.e. "%.6g\n" and a
+// flush (a write system call) per line, serially.  Same bytes here: the values are formatted by n_threads host threads
+// into per-thread buffers and written with one fwrite per buffer.
+namespace
+{
+int
+write_values_text(const double * v, int64_t n, const char * path, int n_threads, char * err)
+{
+  if (n_threads < 1)
+    n_threads = (int)std::max(1u, std::min(std::thread::hardware_concurrency(), 64u));
+  if ((int64_t)n_threads > std::max<int64_t>(1, n / 4096))
+    n_threads = (int)std::max<int64_t>(1, n / 4096);
+  std::vector<std::vector<char>> bufs(n_threads);
+  auto work = [&](int t) {
+    const int64_t lo = n * t / n_threads, hi = n * (t + 1) / n_threads;
+    std::vector<char> & b = bufs[t];
+    b.resize((size_t)(hi - lo) * 26 + 32);
+    size_t pos = 0;
+    for (int64_t i = lo; i < hi; ++i)
+      pos += (size_t)snprintf(b.data() + pos, 26, "%.6g\n", v[i]);
+    b.resize(pos);
+  };
+  std::vector<std::thread> th;
+  for (int t = 1; t < n_threads; ++t)
+    th.emplace_back(work, t);
+  work(0);
+  for (auto & t : th)
+    t.join();
+  FILE * f = fopen(path, "wb");
+  if (!f)
+  {
+    snprintf(err, DOMA_MAX_ERR, "write_values_text: cannot open %s", path);
+    return 9;
+  }
+  bool ok = true;
+  for (auto & b : bufs)
+    ok = ok && fwrite(b.data(), 1, b.size(), f) == b.size();
+  ok = (fclose(f) == 0) && ok;
+  if (!ok)
+  {
+    snprintf(err, DOMA_MAX_ERR, "write_values_text: short write to %s", path);
+    return 9;
+  }
+  return 0;
+}
+} // namespace
+
+int
+doma_b200_write_values_text(const double * values, int64_t n, const char * path, int32_t n_threads)
+{
+  if (!values || n < 0 || !path)
+  {
+    snprintf(g_create_err, DOMA_MAX_ERR, "write_values_text: invalid argument");
+    return 1;
+  }
+  return write_values_text(values, n, path, n_threads, g_create_err);
+}
+
+// A dump = a host snapshot of the state (taken on the calling thread, so the solve may go on and overwrite the device
+// arrays) + the formatting and writing of the files, which runs inline (doma_b200_dump_text) or on a worker thread
+// that the next dump, doma_b200_dump_wait or doma_b200_destroy joins (doma_b200_dump_text_async).
+struct DumpJob
+{
+  std::string base;
+  int64_t N = 0;
+  int n_threads = 0;
+  std::vector<std::vector<double>> flux, dnps;
+  std::thread worker;
+  int rc = 0;
+  char err[DOMA_MAX_ERR] = {0};
+  void run()
+  {
+    for (size_t g = 0; g < flux.size() && !rc; ++g)
+      rc = write_values_text(flux[g].data(), N, (base + "_g" + std::to_string(g) + "_flux.txt").c_str(), n_threads, err);
+    for (size_t d = 0; d < dnps.size() && !rc; ++d)
+      rc = write_values_text(dnps[d].data(), N, (base + "_d" + std::to_string(d) + "_dnps.txt").c_str(), n_threads, err);
+    flux.clear(), dnps.clear();
+  }
+};
+
+namespace
+{
+int
+join_dump(doma_b200_ctx * c)
+{
+  DumpJob * j = (DumpJob *)c->dump_job;
+  if (!j)
+    return 0;
+  if (j->worker.joinable())
+    j->worker.join();
+  const int rc = j->rc;
+  if (rc)
+    memcpy(c->err, j->err, DOMA_MAX_ERR);
+  delete j;
+  c->dump_job = nullptr;
+  return rc;
+}
+
+int
+snapshot_for_dump(doma_b200_ctx * c, DumpJob * j, const char * file_base, int with_dnps, int n_threads)
+{
+  DOMA_CUDA(c, cudaStreamSynchronize(c->stream));
+  const size_t N = (size_t)c->N;
+  j->base = file_base, j->N = c->N, j->n_threads = n_threads;
+  j->flux.resize(c->G);
+  for (int g = 0; g < c->G; ++g)
+  {
+    j->flux[g].resize(N);
+    DOMA_CUDA(c, cudaMemcpy(j->flux[g].data(), c->phi_tot + (size_t)g * N, sizeof(double) * N, cudaMemcpyDeviceToHost));
+  }
+  if (with_dnps && c->D > 0 && c->dnp_cur)
+  {
+    // dumpDNPsToTextFile: num_d_groups = the largest precursor count of any cell's material; a cell whose material has
+    // fewer prints 0 for every precursor group (src/BrickMesh3D.cpp:268-289)
+    std::vector<int32_t> mat(N), nd((size_t)c->M);
+    DOMA_CUDA(c, cudaMemcpy(mat.data(), c->mat, sizeof(int32_t) * N, cudaMemcpyDeviceToHost));
+    DOMA_CUDA(c, cudaMemcpy(nd.data(), c->n_delayed, sizeof(int32_t) * c->M, cudaMemcpyDeviceToHost));
+    int dmax = 0;
+    for (size_t i = 0; i < N; ++i)
+      dmax = std::max(dmax, (int)nd[mat[i]]);
+    j->dnps.resize(dmax);
+    for (int d = 0; d < dmax; ++d)
+    {
+      j->dnps[d].resize(N);
+      DOMA_CUDA(c, cudaMemcpy(j->dnps[d].data(), c->dnp_cur + (size_t)d * N, sizeof(double) * N, cudaMemcpyDeviceToHost));
+      for (size_t i = 0; i < N; ++i)
+        if (nd[mat[i]] != dmax)
+          j->dnps[d][i] = 0.0;
+    }
+  }
+  return 0;
+}
+
+int
+dump_impl(doma_b200_ctx * c, const char * file_base, int with_dnps, int n_threads, bool async)
+{
+  if (!file_base)
+  {
+    snprintf(c->err, DOMA_MAX_ERR, "dump_text: null file base");
+    return 1;
+  }
+  int rc = join_dump(c); // one dump in flight per context; also surfaces the previous one's error
+  if (rc)
+    return rc;
+  DumpJob * j = new DumpJob();
+  if ((rc = snapshot_for_dump(c, j, file_base, with_dnps, n_threads)))
+  {
+    delete j;
+    return rc;
+  }
+  c->dump_job = j;
+  if (async)
+  {
+    j->worker = std::thread([j] { j->run(); });
+    return 0;
+  }
+  j->run();
+  return join_dump(c);
+}
+} // namespace
+
+int
+doma_b200_dump_text(doma_b200_ctx * c, const char * file_base, int32_t with_dnps, int32_t n_threads)
+{
+  ENTER(c);
+  return dump_impl(c, file_base, with_dnps, n_threads, false);
+}
+
+int
+doma_b200_dump_text_async(doma_b200_ctx * c, const char * file_base, int32_t with_dnps, int32_t n_threads)
+{
+  ENTER(c);
+  return dump_impl(c, file_base, with_dnps, n_threads, true);
+}
+
+int
+doma_b200_dump_wait(doma_b200_ctx * c)
+{
+  ENTER(c);
+  return join_dump(c);
 }
 
 // ---- angle sharding across ranks: one in-place ncclAllReduce(phi_cur) per sweep ----

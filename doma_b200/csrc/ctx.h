@@ -87,6 +87,8 @@ struct doma_b200_ctx
   cudaEvent_t ev_q_staged, ev_q_consumed, ev_snap, ev_copied;
   bool async_ready, q_is_staged, copy_pending;
 
+  void * dump_job; // text dump in flight on a worker thread (api.cu, DumpJob), or null
+
   // NCCL (resolved with dlopen at comm_init; see api.cu)
   void * nccl_comm;
   int rank, nranks;

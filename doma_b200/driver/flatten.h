@@ -11,6 +11,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <map>
+#include <string>
 #include <unordered_map>
 #include <vector>
 
@@ -175,11 +176,61 @@ struct DriverConfig
   int tile_y = 0, tile_z = 0; // 0 = library default
   double last_k = 1.0;                // TransportSolver::_k after the last updateEigenvalue
   doma_b200_ctx * live_ctx = nullptr; // context of the solver currently alive (owned by its operator)
+  // --fast-dump: steady / eigenvalue runs write their final text dump through doma_b200_dump_text instead of
+  // BrickMesh::dumpToTextFile (same bytes, tests/test_text_output.py), and computeMGFluxResidual no longer copies
+  // the flux into the per-cell host vectors after every outer iteration.  The geometry kept for the static files:
+  bool fast_dump = false;
+  int geom_dims = 3, geom_groups = 1;
+  std::vector<double> geom_dx, geom_dy, geom_dz;
+  std::vector<unsigned int> geom_block_of_cell;
 };
 inline DriverConfig & config()
 {
   static DriverConfig c;
   return c;
+}
+
+// <base>_dims.txt, _blocks.txt, _meshx/y/z.txt exactly as BrickMesh3D::dumpToTextFile writes them
+// (src/BrickMesh3D.cpp:216-258; 2D: src/BrickMesh2D.cpp:169-205), from the flattened geometry.
+inline void
+writeGeometryFiles(const DriverConfig & c, const std::string & base)
+{
+  const std::size_t nx = c.geom_dx.size(), ny = c.geom_dy.size(), nz = c.geom_dims == 3 ? c.geom_dz.size() : 1;
+  auto centres = [](const std::vector<double> & w) { // the reference's running centre (src/BrickMesh3D.cpp:84-101)
+    std::vector<double> v(w.size());
+    double acc = 0.5 * w[0];
+    for (std::size_t i = 0; i < w.size(); ++i)
+    {
+      v[i] = acc;
+      acc += w[i];
+    }
+    return v;
+  };
+  const auto xc = centres(c.geom_dx), yc = centres(c.geom_dy), zc = c.geom_dims == 3 ? centres(c.geom_dz) : std::vector<double>();
+  std::FILE * f = std::fopen((base + "_dims.txt").c_str(), "w");
+  std::fprintf(f, "num_x: %zu\nnum_y: %zu\n", nx, ny);
+  if (c.geom_dims == 3)
+    std::fprintf(f, "num_z: %zu\n", nz);
+  std::fprintf(f, "num_g: %d\n", c.geom_groups);
+  std::fclose(f);
+  f = std::fopen((base + "_blocks.txt").c_str(), "w");
+  for (unsigned int b : c.geom_block_of_cell)
+    std::fprintf(f, "%u\n", b);
+  std::fclose(f);
+  std::vector<double> v(nx * ny * nz);
+  for (int axis = 0; axis < c.geom_dims; ++axis)
+  {
+    for (std::size_t k = 0, n = 0; k < nz; ++k)
+      for (std::size_t j = 0; j < ny; ++j)
+        for (std::size_t i = 0; i < nx; ++i, ++n)
+          v[n] = axis == 0 ? xc[i] : (axis == 1 ? yc[j] : zc[k]);
+    const char * names[] = {"_meshx.txt", "_meshy.txt", "_meshz.txt"};
+    if (doma_b200_write_values_text(v.data(), (int64_t)v.size(), (base + names[axis]).c_str(), 0) != 0)
+    {
+      std::fprintf(stderr, "Error: cannot write %s%s\n", base.c_str(), names[axis]);
+      std::exit(1);
+    }
+  }
 }
 
 // NCCL unique-id exchange between the ranks of one box through a file (rank 0 writes, others poll).

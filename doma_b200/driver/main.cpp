@@ -6,6 +6,8 @@
 // (solver{2,3}d_b200.cpp).  Extra flags:
 //   --impl reference     run the unmodified OpenMP solver instead (same binary, for A/B checks)
 //   --no-output          do not write the text dumps
+//   --fast-dump          steady / eigenvalue runs: final dump through doma_b200_dump_text (same bytes, multi-threaded),
+//                        and no per-outer-iteration copy of the flux into the per-cell host vectors
 //   --tile TYxTZ         KBA tile override
 // One process per GPU: with RANK / WORLD_SIZE / LOCAL_RANK in the environment (torchrun --no-python,
 // or any launcher) the ordinates are sharded over the ranks and phi is all-reduced with NCCL;
@@ -92,6 +94,7 @@ main(int argc, char ** argv)
     else if (a == "--verbose") verbose = true;
     else if (a == "--impl") impl = next();
     else if (a == "--no-output") output = false;
+    else if (a == "--fast-dump") config().fast_dump = true;
     else if (a == "--tile")
     {
       const std::string t = next();
@@ -103,7 +106,7 @@ main(int argc, char ** argv)
     }
     else
     {
-      std::cerr << "usage: doma_b200_driver -i case.xml [-n threads] [--verbose] [--impl b200|reference] [--no-output] [--tile TYxTZ]"
+      std::cerr << "usage: doma_b200_driver -i case.xml [-n threads] [--verbose] [--impl b200|reference] [--no-output] [--fast-dump] [--tile TYxTZ]"
                 << std::endl;
       std::exit(1);
     }

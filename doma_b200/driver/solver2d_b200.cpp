@@ -90,6 +90,14 @@ ensureContext2D(const B200Op2D & op, BrickMesh2D & mesh_unused, FlatProblem & fl
     for (std::size_t c = 0; c < _mesh._cells.size(); ++c)                                                        \
       flat.mat_of_cell[c] = flat.materialIndex(_mesh._cells[c]._block_id);                                       \
     flat.setQuadrature(_angular_quad, config().rank);                                                            \
+    if (config().fast_dump)                                                                                      \
+    {                                                                                                            \
+      auto & cf = config();                                                                                      \
+      cf.geom_dims = flat.dims, cf.geom_groups = static_cast<int>(_num_groups);                                  \
+      cf.geom_dx = flat.dx, cf.geom_dy = flat.dy, cf.geom_dz = flat.dz;                                          \
+      cf.geom_block_of_cell.clear();                                                                             \
+      for (const auto & cell : _mesh._cells) cf.geom_block_of_cell.push_back(cell._block_id);                    \
+    }                                                                                                            \
     return ensureContext2D(_eq_system, _mesh, flat);                                                             \
   }()
 
@@ -220,6 +228,9 @@ B200TransportSolver2D::computeMGFluxResidual()
   double r = 0.0;
   check(doma_b200_mg_residual(ctx, &r), ctx, "doma_b200_mg_residual");
   // the loops dump the mesh right after this member (2D:61-75, 292-306): refresh the host copy
+  // (not with --fast-dump in steady / eigenvalue runs: the final dump then comes from doma_b200_dump_text)
+  if (config().fast_dump && _mode != RunMode::Transient)
+    return r;
   auto & buf = _eq_system.staging;
   buf.resize(_mesh._cells.size());
   for (unsigned int g = 0; g < _num_groups; ++g)
@@ -251,11 +262,18 @@ runB200Solver2D(BrickMesh2D & mesh, const InputParameters & params, bool verbose
 {
   B200TransportSolver2D solver(mesh, params, verbose, 1u);
   bool ok = false;
+  const bool fast = config().fast_dump && params._mode != RunMode::Transient && !out_base.empty();
   switch (params._mode)
   {
-    case RunMode::FixedSrc: ok = solver.solveFixedSource(out_base); break;
-    case RunMode::Eigen: ok = solver.solveEigenvalue(out_base); break;
+    case RunMode::FixedSrc: ok = solver.solveFixedSource(fast ? std::string("") : out_base); break;
+    case RunMode::Eigen: ok = solver.solveEigenvalue(fast ? std::string("") : out_base); break;
     case RunMode::Transient: ok = solver.solveTransient(out_base); break;
+  }
+  if (fast && ok && config().live_ctx)
+  {
+    // the dump the reference's loop would have made on convergence (3D:74-75, 305-306), same bytes
+    writeGeometryFiles(config(), out_base);
+    check(doma_b200_dump_text(config().live_ctx, out_base.c_str(), 0, 0), config().live_ctx, "doma_b200_dump_text");
   }
   if (k_out)
     *k_out = config().last_k;

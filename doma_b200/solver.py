@@ -36,8 +36,10 @@ class Trace:
 class TransportSolver:
     def __init__(self, ctx: abi.Context, params: InputParameters, verbose: bool = False,
                  allreduce: Optional[Callable[[abi.Context], None]] = None, log: Callable[[str], None] = None,
-                 fused_si: bool = False):
+                 fused_si: bool = False, output_base: str = "", problem: Optional[abi.Problem] = None):
         self.ctx = ctx
+        # text dumps at the reference's dump points (3D:75,112,127-128,306); "" = none, as in the reference
+        self.output_base, self.problem = output_base, problem
         self.num_groups = params.num_groups
         self.mode = params.mode
         self.sit, self.smi = params.fs_tol, params.fs_max_it
@@ -97,7 +99,13 @@ class TransportSolver:
         return ok
 
     # --- solveFixedSource (3D:262-316) -----------------------------------------------------------
-    def solve_fixed_source(self, t: float = 0.0) -> bool:
+    def _dump(self, base: str, only_flux: bool = False, dnps: bool = False):
+        from .output import dump_to_text_file
+        # overlapped with the next time step / the caller's next work; solve() waits for the last one
+        dump_to_text_file(self.ctx, self.problem, base, only_flux, with_dnps=dnps, asynchronous=True)
+
+    def solve_fixed_source(self, t: float = 0.0, output_base: Optional[str] = None) -> bool:
+        output_base = (self.output_base if self.mode == abi.MODE_FIXED else "") if output_base is None else output_base
         if self.mode != abi.MODE_TRANSIENT:
             self.initialize_solve()
         it, res = 0, 0.0
@@ -115,6 +123,8 @@ class TransportSolver:
         ok = it < self.mgi
         if ok and self.num_groups > 1:
             self._log(f"MGI converged after {it} iterations with a residual of {res!r}")
+        if ok and output_base:
+            self._dump(output_base)                                        # 3D:305-306
         if not ok:
             self._log(f"MGI failed to converge after {it} iterations with a residual of {res!r}")
         return ok
@@ -140,6 +150,8 @@ class TransportSolver:
         ok = it < self.mgi
         self._log(f"PI {'converged' if ok else 'failed to converge'} after {it} iterations with a flux shape residual of "
                   f"{shape_res!r} and a k residual of {k_diff!r}." + (f"\nConverged value of k = {self.k!r}" if ok else ""))
+        if ok and self.output_base:
+            self._dump(self.output_base)                                   # 3D:74-75
         return ok
 
     # --- solveTransient (3D:88-138) --------------------------------------------------------------
@@ -149,12 +161,16 @@ class TransportSolver:
         else:
             # ics="steady" indexes empty vectors in the reference (undefined behaviour)
             raise NotImplementedError("ics='steady' is undefined behaviour in the reference; unsupported")
+        if self.output_base:
+            self._dump(self.output_base)                                   # 3D:112, the initial condition
         t = 0.0
         for step in range(self.t_steps):
             self._log(f"Solving timestep {step}...")
-            if not self.solve_fixed_source(t):
+            if not self.solve_fixed_source(t, ""):
                 return False
             self.ctx.step_dnps()
+            if self.output_base:
+                self._dump(f"{self.output_base}_t{step}", only_flux=True, dnps=True)   # 3D:127-128
             if on_step is not None:
                 on_step(step, self)
             if step != self.t_steps - 1:
@@ -163,11 +179,15 @@ class TransportSolver:
         return True
 
     def solve(self) -> bool:
-        if self.mode == abi.MODE_FIXED:
-            return self.solve_fixed_source()
-        if self.mode == abi.MODE_EIGEN:
-            return self.solve_eigenvalue()
-        return self.solve_transient()
+        try:
+            if self.mode == abi.MODE_FIXED:
+                return self.solve_fixed_source()
+            if self.mode == abi.MODE_EIGEN:
+                return self.solve_eigenvalue()
+            return self.solve_transient()
+        finally:
+            if self.output_base and self.ctx.has("dump_wait"):
+                self.ctx.dump_wait()
 
     def flux(self) -> np.ndarray:
         return self.ctx.flux()

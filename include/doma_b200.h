@@ -133,6 +133,21 @@ int doma_b200_stage_q_from_host(doma_b200_ctx * ctx, const double * q_host);
 int doma_b200_sweep_from_host_async(doma_b200_ctx * ctx, int32_t g, const double * q_host, double * phi_cur_out);
 int doma_b200_host_wait(doma_b200_ctx * ctx);
 
+/* text output -------------------------------------------------------------------------------------- */
+/* The flux (and precursor) files of BrickMesh3D::dumpToTextFile / dumpDNPsToTextFile (src/BrickMesh3D.cpp:216-295;
+ * 2D: src/BrickMesh2D.cpp): "<base>_g<g>_flux.txt" for every group and, with with_dnps != 0 in a transient context,
+ * "<base>_d<d>_dnps.txt", one "%.6g" value per line in reference cell order - byte for byte what the reference's
+ * `stream << std::setprecision(6) << v << std::endl` loop writes, formatted by n_threads host threads (0 = all cores).
+ * The geometry files (_dims, _blocks, _meshx/y/z) do not depend on the solve and stay with the host front end. */
+int doma_b200_dump_text(doma_b200_ctx * ctx, const char * file_base, int32_t with_dnps, int32_t n_threads);
+/* The same, overlapped with whatever the caller does next: the state is copied to the host before the call returns
+ * (so the solve may continue), the files are formatted and written on a worker thread.  One dump in flight per context:
+ * the next dump, doma_b200_dump_wait and doma_b200_destroy wait for it; its error, if any, is returned by that call. */
+int doma_b200_dump_text_async(doma_b200_ctx * ctx, const char * file_base, int32_t with_dnps, int32_t n_threads);
+int doma_b200_dump_wait(doma_b200_ctx * ctx);
+/* the formatter on its own (pure host code, needs no context or device) */
+int doma_b200_write_values_text(const double * values, int64_t n, const char * path, int32_t n_threads);
+
 /* sourceIteration(g) (3D:458-497) as ONE call (the fused inner iteration of SURVEY.md 8f-1):
  *   do { sweep(g); all-reduce phi_cur over ranks; residual = computeScatteringResidual(g); updateScatteringSource(g); it++ }
  *   while (it < max_it && tol < residual);

@@ -57,6 +57,7 @@ struct RunResult
 };
 
 std::string g_scratch = "/tmp";
+std::string g_text_base; // --text <base>: let the reference write its own text dumps there (fixtures for the output path)
 
 template <typename Solver>
 RunResult
@@ -66,10 +67,10 @@ runSolver(Solver & solver, RunMode mode)
   const double t0 = omp_get_wtime();
   switch (mode)
   {
-    case RunMode::FixedSrc: r.ok = solver.solveFixedSource(""); break;
-    case RunMode::Eigen: r.ok = solver.solveEigenvalue(""); break;
+    case RunMode::FixedSrc: r.ok = solver.solveFixedSource(g_text_base); break;
+    case RunMode::Eigen: r.ok = solver.solveEigenvalue(g_text_base); break;
     // solveTransient always writes "<base>_t<N>_g<g>_flux.txt" text dumps; send them to a scratch dir.
-    case RunMode::Transient: r.ok = solver.solveTransient(g_scratch + "/tr"); break;
+    case RunMode::Transient: r.ok = solver.solveTransient(g_text_base.empty() ? g_scratch + "/tr" : g_text_base); break;
   }
   r.seconds = omp_get_wtime() - t0;
   r.k = solver._k;
@@ -162,13 +163,20 @@ main(int argc, char ** argv)
 {
   if (argc < 4)
   {
-    std::cerr << "usage: ref_harness <case.xml> <threads> <out_dir> [--no-dump]\n";
+    std::cerr << "usage: ref_harness <case.xml> <threads> <out_dir> [--no-dump] [--text <file base>]\n";
     return 2;
   }
   const std::string xml = argv[1];
   const int threads = std::max(1, std::atoi(argv[2]));
   const std::string out = argv[3];
-  const bool dump = !(argc > 4 && std::string(argv[4]) == "--no-dump");
+  bool dump = true;
+  for (int i = 4; i < argc; ++i)
+  {
+    if (std::string(argv[i]) == "--no-dump")
+      dump = false;
+    else if (std::string(argv[i]) == "--text" && i + 1 < argc)
+      g_text_base = argv[++i];
+  }
   std::filesystem::create_directories(out);
   g_scratch = out + "/scratch";
   std::filesystem::create_directories(g_scratch);

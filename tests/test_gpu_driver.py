@@ -41,3 +41,29 @@ def test_driver_reproduces_reference(name, tmp_path):
             ref = g["phi"][grp]
             big = np.abs(ref) > 1e-30
             assert np.max(np.abs(phi[big] - ref[big]) / np.abs(ref[big])) < 2e-5
+
+
+@pytest.mark.parametrize("name", ["k1_r0_s3", "test2d_r0"])
+def test_driver_fast_dump_writes_the_reference_files(name, tmp_path):
+    """--fast-dump: the final dump comes from doma_b200_dump_text + the flattened geometry instead of
+    BrickMesh::dumpToTextFile; the two runs of the same binary must leave byte-identical files, and for the case
+    with a reference text fixture (tests/golden/text) the reference's own bytes."""
+    import tarfile
+    outs = []
+    for flags in ([], ["--fast-dump"]):
+        d = tmp_path / ("fast" if flags else "plain")
+        d.mkdir()
+        xml = d / (name + ".xml")
+        xml.write_text(open(golden_case_path(name)).read())
+        r = subprocess.run([DRIVER, "-i", str(xml)] + flags, capture_output=True, text=True, timeout=600)
+        assert "ok=1" in r.stdout.rsplit("DRIVER", 1)[1], r.stdout[-2000:] + r.stderr[-2000:]
+        outs.append({f[len(name):]: open(d / f, "rb").read() for f in os.listdir(d) if f.endswith(".txt")})
+    plain, fast = outs
+    assert sorted(plain) == sorted(fast) and len(fast) >= 5
+    assert not [n for n in plain if plain[n] != fast[n]]
+    fixture = os.path.join(ROOT, "tests", "golden", "text", name + ".tar.gz")
+    if os.path.exists(fixture):
+        with tarfile.open(fixture) as tar:
+            ref = {m.name[len("ref"):]: tar.extractfile(m).read() for m in tar.getmembers()}
+        assert sorted(ref) == sorted(fast)
+        assert not [n for n in ref if ref[n] != fast[n]]
