@@ -92,6 +92,43 @@ def test_single_sweep_matches_oracle(shape, dims, scheme, npol, nazi, tile, cuda
     assert ctx.info(abi.INFO_SWEEP_VARIANT) == 1
 
 
+@pytest.mark.parametrize("seed", range(24))
+def test_random_problems_full_step_matches_oracle(seed, cuda_lib, oracle_lib):
+    """Seeded random problems (dimension, scheme, ragged shape, tile, quadrature order, group count, void material,
+    automatic or forced tile) driven through one full Gauss-Seidel step - source build, sweep, residual, scattering
+    update per group, then the multigroup residual - on both libraries: fluxes to 1e-10, residuals to 1e-12."""
+    rng = np.random.default_rng(1000 + seed)
+    dims = int(rng.integers(2, 4))
+    shape = tuple(int(v) for v in rng.integers(1, 41, 3))
+    G = int(rng.integers(1, 4))
+    prob = random_problem(shape, G=G, dims=dims, scheme=int(rng.integers(0, 2)), npol=int(rng.integers(1, 4)),
+                          nazi=int(rng.integers(1, 4)), seed=seed, n_mat=int(rng.integers(1, 5)), void=bool(rng.integers(0, 2)))
+    tile = (int(rng.choice([1, 2, 3, 4])), int(rng.integers(1, 10))) if rng.random() < 0.7 else None
+    phi0 = 10.0 ** rng.uniform(-10, 1, (G, prob.n_cells))
+    res = []
+    for lib in (oracle_lib, cuda_lib):
+        ctx = abi.Context(prob, lib)
+        if lib is cuda_lib and tile:
+            ctx.set_tile(8, tile[0], tile[1] if dims == 3 else 1)
+        ctx.reset_state(0.0)
+        for g in range(G):
+            ctx.set_array(abi.ARR_PHI_TOT, g, phi0[g])
+        r = []
+        for g in range(G):
+            ctx.update_mg_source(g, 0.0)
+            for _ in range(2):
+                ctx.sweep(g)
+                r.append(ctx.scatter_residual(g))
+                ctx.update_scatter_source(g)
+        r.append(ctx.mg_residual())
+        res.append((np.stack([ctx.get_array(abi.ARR_PHI_TOT, g) for g in range(G)]), np.array(r)))
+    (po, ro), (pc, rc) = res
+    assert np.all(np.isfinite(po))
+    scale = np.maximum(np.abs(po), 1e-14 * np.abs(po).max(axis=1, keepdims=True))   # see tests/test_gpu_full_cases.py FLUX_FLOOR
+    assert float(np.max(np.abs(pc - po) / np.maximum(scale, 1e-300))) <= FLUX_RTOL
+    np.testing.assert_allclose(rc, ro, rtol=1e-11, atol=1e-300)
+
+
 def test_sweep_from_host_equals_resident(cuda_lib):
     prob = random_problem((17, 9, 6), G=1, seed=5)
     q = np.random.default_rng(2).uniform(0, 1, prob.n_cells)
