@@ -68,48 +68,72 @@ doma_build_units(doma_b200_ctx * c, int V)
   std::vector<int> uo;
   std::vector<double> mu, eta, xi, w;
   std::vector<SweepUnit> units;
+  // ordinates of every octant, in the context's order
+  std::vector<int> by_oct[8];
+  for (int n = 0; n < c->n_ord; ++n)
+    by_oct[c->h_ord_octant[n]].push_back(n);
+  size_t most = 0;
   for (int oct = 0; oct < 8; ++oct)
-  {
-    std::vector<int> idx;
-    for (int n = 0; n < c->n_ord; ++n)
-      if (c->h_ord_octant[n] == oct)
-        idx.push_back(n);
-    if (idx.empty())
-      continue;
-    const int cnt = (int)idx.size();
-    const int nb = (cnt + L - 1) / L;
-    int pos = 0;
-    for (int b = 0; b < nb; ++b)
+    most = std::max(most, by_oct[oct].size());
+  auto push_lane = [&](int n) {
+    if (n >= 0)
     {
-      const int sz = cnt / nb + (b < cnt % nb ? 1 : 0);
-      units.push_back(SweepUnit{oct, sz});
+      // parallelSweepOctant takes std::abs of each component (src/TransportSolver3D.cpp:645-649)
+      mu.push_back(fabs(c->h_mu[n]));
+      eta.push_back(fabs(c->h_eta[n]));
+      xi.push_back(fabs(c->h_xi[n]));
+      w.push_back(c->h_w[n]);
+    }
+    else
+    {
+      mu.push_back(1.0);
+      eta.push_back(1.0);
+      xi.push_back(1.0);
+      w.push_back(0.0);
+    }
+  };
+  // <= 16 ordinates per octant (the shipped assembly cases): two octants that differ only in the x direction share a
+  // warp, 16 lanes each (sweep.cu, PAIR) - otherwise every warp would run half empty
+  const bool paired = V == 1 && most > 0 && most <= DOMA_LANES / 2 && !getenv("DOMA_B200_NO_PAIR");
+  if (paired)
+  {
+    for (int oct = 0; oct < 4; ++oct) // bit 2 clear: x ascending; its partner is oct | 4
+    {
+      const std::vector<int> &ia = by_oct[oct], &ib = by_oct[oct | 4];
+      if (ia.empty() && ib.empty())
+        continue;
+      units.push_back(SweepUnit{oct, (int)(ia.size() + ib.size())});
       uo.push_back(oct);
-      for (int v = 0; v < V; ++v)
-      {
-        const int vsz = sz / V + (v < sz % V ? 1 : 0);
-        for (int l = 0; l < DOMA_LANES; ++l)
-        {
-          if (l < vsz)
-          {
-            const int n = idx[pos + l];
-            // parallelSweepOctant takes std::abs of each component (src/TransportSolver3D.cpp:645-649)
-            mu.push_back(fabs(c->h_mu[n]));
-            eta.push_back(fabs(c->h_eta[n]));
-            xi.push_back(fabs(c->h_xi[n]));
-            w.push_back(c->h_w[n]);
-          }
-          else
-          {
-            mu.push_back(1.0);
-            eta.push_back(1.0);
-            xi.push_back(1.0);
-            w.push_back(0.0);
-          }
-        }
-        pos += vsz;
-      }
+      for (int l = 0; l < DOMA_LANES / 2; ++l)
+        push_lane(l < (int)ia.size() ? ia[l] : -1);
+      for (int l = 0; l < DOMA_LANES / 2; ++l)
+        push_lane(l < (int)ib.size() ? ib[l] : -1);
     }
   }
+  else
+    for (int oct = 0; oct < 8; ++oct)
+    {
+      const std::vector<int> & idx = by_oct[oct];
+      if (idx.empty())
+        continue;
+      const int cnt = (int)idx.size();
+      const int nb = (cnt + L - 1) / L;
+      int pos = 0;
+      for (int b = 0; b < nb; ++b)
+      {
+        const int sz = cnt / nb + (b < cnt % nb ? 1 : 0);
+        units.push_back(SweepUnit{oct, sz});
+        uo.push_back(oct);
+        for (int v = 0; v < V; ++v)
+        {
+          const int vsz = sz / V + (v < sz % V ? 1 : 0);
+          for (int l = 0; l < DOMA_LANES; ++l)
+            push_lane(l < vsz ? idx[pos + l] : -1);
+          pos += vsz;
+        }
+      }
+    }
+  c->units_paired = paired;
   c->device_bytes -= c->face_bytes;
   free_dev(c->unit_octant), free_dev(c->u_mu), free_dev(c->u_eta), free_dev(c->u_xi), free_dev(c->u_w);
   free_dev(c->face_x), free_dev(c->face_y), free_dev(c->face_z);
@@ -143,10 +167,10 @@ doma_build_units(doma_b200_ctx * c, int V)
   // exposes n_tiles / n_hyperplanes independent tiles on average; with few units per GPU (angle sharding over
   // 4-8 ranks, or 16 ordinates per octant) the wavefront starves.  Measured on B200 at 256^3 (profiles/
   // r01_sweep_experiments.txt): 16 and 8 units -> 8x4x8, 4 units -> 8x4x4, 2 units -> 8x4x2.
-  static const int cand3[][2] = {{4, 8}, {4, 4}, {4, 2}, {2, 2}};
+  static const int cand3[][2] = {{4, 8}, {4, 4}, {4, 2}, {2, 2}, {4, 1}, {2, 1}};
   static const int cand2[][2] = {{4, 1}, {2, 1}, {1, 1}};
   const int(*cand)[2] = c->dims == 3 ? cand3 : cand2;
-  const int n_cand = c->dims == 3 ? 4 : 3;
+  const int n_cand = c->dims == 3 ? 6 : 3;
   // resident warps are 16 per SM (4 CTAs x 4 warps); the measured optimum sits at 1.0-1.8 tasks in flight per
   // resident warp (2 units: 8x4x4 0.70 -> 7.53 ms, 8x4x2 1.00 -> 7.02 ms, 8x2x2 1.55 -> 7.61 ms), hence 15 not 16
   const double want = 15.0 * c->n_sms;

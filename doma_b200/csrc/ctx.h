@@ -56,6 +56,7 @@ struct doma_b200_ctx
   int n_units;
   SweepUnit * h_units; // host copy
   int * unit_octant;   // [U]
+  bool units_paired;   // every unit carries two octants that differ in x, 16 lanes each (sweep.cu, PAIR)
   double *u_mu, *u_eta, *u_xi, *u_w; // [U][V][32] absolute direction cosines; padding lanes: 1,1,1,w=0
 
   // sweep scratch

@@ -6,7 +6,7 @@ def load(lib):
     out=subprocess.run(f"cuobjdump -sass {lib}",shell=True,capture_output=True,text=True).stdout
     lines=out.split('\n'); ins=[]; on=False
     for i,l in enumerate(lines):
-        if 'Function :' in l: on = 'sweep_kernelILi3ELi1' in l
+        if 'Function :' in l: on = ('sweep_kernelILi3ELi1ELb0' in l or ('sweep_kernelILi3ELi1E' in l and 'ELb' not in l))
         if not on: continue
         m=re.match(r'\s+/\*([0-9a-f]{4})\*/\s+(.*?);\s+/\* (0x[0-9a-f]+) \*/',l)
         if m:

@@ -8,7 +8,7 @@ import numpy as np
 import doma_b200 as d
 from doma_b200 import abi
 cases = os.path.join(ROOT, "tests", "golden", "cases")
-for f, tiles in [("full_tr2d_1step.xml", [(0, 0), (1, 1), (2, 1), (4, 1)]), ("full_asm_fs_3outer.xml", [(0, 0), (2, 2), (4, 2), (4, 4), (2, 4)]),
+for f, tiles in [("full_tr2d_1step.xml", [(0, 0), (1, 1), (2, 1), (4, 1)]), ("full_asm_fs_3outer.xml", [(0, 0), (2, 2), (4, 2), (4, 4), (2, 4), (2, 1), (4, 1), (1, 2)]),
                  ("full_k1.xml", [(0, 0), (2, 2), (4, 2), (4, 4), (4, 8)])]:
     params, prob = d.load_case(os.path.join(cases, f))
     for ty, tz in tiles:
