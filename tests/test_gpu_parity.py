@@ -129,6 +129,28 @@ def test_random_problems_full_step_matches_oracle(seed, cuda_lib, oracle_lib):
     np.testing.assert_allclose(rc, ro, rtol=1e-11, atol=1e-300)
 
 
+@pytest.mark.parametrize("dims,scheme,shape", [(3, 1, (21, 10, 9)), (3, 0, (8, 8, 8)), (2, 1, (30, 17, 1)), (3, 1, (5, 3, 2))])
+def test_octant_pairing_equals_unpaired(dims, scheme, shape, cuda_lib, oracle_lib, monkeypatch):
+    """<= 16 ordinates per octant: two x-mirrored octants share a warp (sweep.cu PAIR).  Same flux as the unpaired
+    units (DOMA_B200_NO_PAIR=1) and as the oracle, half the units."""
+    prob = random_problem(shape, G=1, dims=dims, scheme=scheme, npol=2, nazi=3, seed=shape[0])     # 12 per octant in 3D
+    q = 10.0 ** np.random.default_rng(9).uniform(-11, 1, prob.n_cells)
+    def run(lib):
+        ctx = abi.Context(prob, lib)
+        ctx.reset_state(0.0)
+        ctx.set_array(abi.ARR_Q, 0, q)
+        ctx.sweep(0)
+        return ctx.get_array(abi.ARR_PHI_CUR, 0), (ctx.info(abi.INFO_N_UNITS) if lib is cuda_lib else 0)
+    paired, n_paired = run(cuda_lib)
+    monkeypatch.setenv("DOMA_B200_NO_PAIR", "1")
+    plain, n_plain = run(cuda_lib)
+    monkeypatch.delenv("DOMA_B200_NO_PAIR")
+    ref, _ = run(oracle_lib)
+    assert n_plain == 2 * n_paired and n_paired == (4 if dims == 3 else 2)
+    assert relmax(paired, plain) <= 1e-13
+    assert relmax(paired, ref) <= FLUX_RTOL
+
+
 def test_sweep_from_host_equals_resident(cuda_lib):
     prob = random_problem((17, 9, 6), G=1, seed=5)
     q = np.random.default_rng(2).uniform(0, 1, prob.n_cells)
