@@ -113,6 +113,36 @@ def run_reference_sample(n, G, steps, warmup, threads, mode="B", sweeps=1):
                             f"OpenMP {threads} threads, solve time only, mean of {steps} run(s) after {warmup} warm-up")
 
 
+def parity_check(ctx, n, G, rank, world, emulated):
+    """phi_tot of this rank against the reference digest of the same solve; all ranks must hold the same bits."""
+    import zlib
+
+    import numpy as np
+
+    from doma_b200.digest import SYNTHETIC_FLOOR, flux_errors, within_bounds
+
+    phi = ctx.flux()                                    # [G, N]; collective when the cell phases are sharded
+    crc = zlib.crc32(phi.tobytes())
+    crcs = [crc]
+    if world > 1:
+        import torch.distributed as dist
+
+        crcs = [None] * world
+        dist.all_gather_object(crcs, crc)
+    out = {"checked": False, "n_ranks": world, "ranks_bit_identical": len(set(crcs)) == 1}
+    path = os.path.join(ROOT, "tests", "golden", "full", "syn256_b.npz")
+    if emulated > 1:
+        out["why"] = "emulated shard: only a subset of the ordinates is swept"
+    elif n != 256 or G != 8 or not os.path.exists(path):
+        out["why"] = f"the committed reference digest is of the 256^3 x 8-group workload, not {n}^3 x {G}"
+    elif rank == 0:
+        errs = flux_errors(phi, np.load(path), 3, SYNTHETIC_FLOOR)
+        out.update(checked=True, vs="digest of the unmodified reference on this workload (tests/golden/full/syn256_b.npz)",
+                   max_err=errs["sample_max"], median_err=errs["sample_median"], errors=errs, tol=1e-10,
+                   floor_frac_of_phi_max=SYNTHETIC_FLOOR, ok=bool(within_bounds(errs)) and out["ranks_bit_identical"])
+    return out
+
+
 def host_threads():
     n = os.cpu_count() or 1
     try:
@@ -132,7 +162,9 @@ def main():
     ap.add_argument("--groups", type=int, default=8)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--tile", default="", help="TYxTZ override of the KBA tile, e.g. 4x8")
-    ap.add_argument("--ref-n", type=int, default=64, help="cells per axis of the bounded CPU sample")
+    ap.add_argument("--variant", default="auto", choices=["auto", "flags", "ll"],
+                    help="face hand-over protocol of the sweep kernel (doma_b200_set_sweep_variant); tuning aid")
+    ap.add_argument("--ref-n", type=int, default=96, help="cells per axis of the bounded CPU sample")
     ap.add_argument("--cpu-n", type=int, default=128, help="cells per axis of the cpu_baseline sample (4 sweeps of group 0)")
     ap.add_argument("--emulate-world", type=int, default=0,
                     help="tuning aid, 1 GPU only: sweep rank 0's ordinate shard of a W-rank run (no all-reduce); "
@@ -142,6 +174,7 @@ def main():
                          "driver's sequence) instead of doma_b200_source_iteration")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="skip the comparison with the reference digest after the first warm-up step")
     a = ap.parse_args()
     a.warmup = max(a.warmup, 3) if a.impl == "b200" else max(a.warmup, 1)
 
@@ -149,10 +182,18 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     G, n = a.groups, a.n
-    config = {"workload": f"synthetic 3D {n}^3 cells, {G} groups, S16 GC quadrature (np=na=8, 512 ordinates), TWDD, Mode B "
-                          f"(one sweep per group, Gauss-Seidel source build between)",
+
+    def workload(cells_per_axis):
+        return (f"synthetic 3D {cells_per_axis}^3 cells, {G} groups, S16 GC quadrature (np=na=8, 512 ordinates), TWDD, Mode B "
+                f"(one sweep per group, Gauss-Seidel source build between)")
+
+    config = {"workload": workload(n),
               "cells": n ** 3, "ordinates": 512, "groups": G, "parallelism": f"angle-sharded x{world}" if world > 1 else "1 GPU",
-              "l2": "working set (face planes + flux arrays, > 1 GB) exceeds the 126 MB L2; no explicit flush"}
+              "l2": "working set (face planes + flux arrays, > 1 GB) exceeds the 126 MB L2; no explicit flush",
+              # identical in both arms, so that the two config objects compare equal AND say what the CPU arm times
+              "reference_arm_sample": f"--impl reference times the unmodified reference on a bounded sample of this workload: "
+                                      f"{a.ref_n}^3 cells of the same recipe (same materials, quadrature, Mode B step over all "
+                                      f"{G} groups); its rate is flat in the mesh size (DESIGN.md 6)"}
 
     if a.impl == "reference":
         if rank != 0:
@@ -162,11 +203,17 @@ def main():
         if v is None:
             print(json.dumps({"impl": "reference", "unavailable": desc}))
             return 0
+        # the line names the mesh that was actually timed: the metric is a rate (updates/s), the reference's rate is flat
+        # in the mesh size (3.7e8 at 64^3, 3.5e8 at 128^3 on 16 threads, 7.2e7 at 256^3 on this container's 8 vCPU), and
+        # a 256^3 Mode-B step costs it ~3 minutes and 14 GB on 16 threads - outside a K-step arm's budget
+        timed = {"cells": a.ref_n ** 3, "workload": workload(a.ref_n), "updates_per_step": float(a.ref_n) ** 3 * 512 * G}
         print(json.dumps({
             "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
             "warmup": a.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-            "dtype": "f64", "data": "synthetic", "config": config,
-            "cpu_baseline": {"value": v, "unit": UNIT, "cores": T, "kind": "reference", "sample": desc},
+            "dtype": "f64", "data": "synthetic", "config": config, "timed": timed,
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": T, "kind": "reference", "sample": desc,
+                             "note": "the same unmodified reference on the full 256^3 x 8 groups x 512 ordinates step: 953 s on 8 vCPU "
+                                     "(7.2e7 updates/s, tests/golden/full/syn256_b.npz ref_seconds)"},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
         return 0
 
@@ -196,6 +243,7 @@ def main():
     ctx = abi.Context(prob)
     stream = torch.cuda.Stream(device=local)
     ctx.set_stream(stream.cuda_stream)      # the context launches on this stream, so torch events see its kernels
+    ctx.set_sweep_variant({"auto": abi.SWEEP_AUTO, "flags": abi.SWEEP_FLAGS, "ll": abi.SWEEP_LL}[a.variant])
     if a.tile:
         ty, tz = [int(v) for v in a.tile.lower().split("x")]
         ctx.set_tile(8, ty, tz)
@@ -230,8 +278,13 @@ def main():
             dist.barrier()
 
     ctx.reset_state(0.0)
-    for _ in range(a.warmup):
+    parity = None
+    for w_i in range(a.warmup):
         step()
+        if w_i == 0 and not a.no_parity:
+            # after ONE step from the zero state the context holds exactly the Mode-B solve whose digest the unmodified
+            # reference wrote (tests/golden/full/syn256_b.npz): compare, outside the timed region, at every rank count
+            parity = parity_check(ctx, n, G, rank, world, a.emulate_world)
     barrier()
     sampler = ClockSampler(local)
     if rank == 0:
@@ -320,28 +373,36 @@ def main():
     peak, peak_src = measured_peaks()
     upd_per_launch = float(N) * prob.n_ord
     achieved = upd_per_launch * BYTES_PER_UPDATE / (mean_sweep_ms * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": "sweep_kernel<3,TWDD>", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                "algorithmic_bytes_per_update": BYTES_PER_UPDATE, "updates_per_launch": upd_per_launch,
-                "launch_ms": mean_sweep_ms, "kernel_updates_per_s": upd_per_launch / (mean_sweep_ms * 1e-3),
+    kernel_rate = upd_per_launch / (mean_sweep_ms * 1e-3)
+    sm_mhz = (clocks or {}).get("sm_mhz") or 1965.0
+    n_sms = torch.cuda.get_device_properties(local).multi_processor_count
+    prof = {}
+    try:
+        prof = json.load(open(os.path.join(ROOT, "profiles", "sweep_traffic.json")))
+    except Exception:
+        pass
+    per_n = (prof.get("per_n_gpus") or {}).get(str(a.emulate_world if a.emulate_world > 1 else world)) or {}
+    fp64_inst = float(prof.get("fp64_inst_per_update") or FP64_INST_PER_UPDATE)
+    # The roof that binds is FP64 issue: lane-instructions of the FP64 pipe per second against
+    # 64 lanes per SM per clock (an FMA counts once).  The HBM model north_star names (48 B per update) is kept beside it.
+    fp64_achieved = kernel_rate * fp64_inst
+    fp64_peak = FP64_WARP_INST_PER_CLK_SM * 32.0 * n_sms * sm_mhz * 1e6
+    roofline = {"bound": "fp64_issue", "kernel": "sweep_kernel<3,TWDD>", "achieved": fp64_achieved / 1e12, "peak": fp64_peak / 1e12,
+                "unit": "T lane-instructions/s of the FP64 pipe (an FMA counts once)", "frac": fp64_achieved / fp64_peak,
+                "fp64_pipe_frac": fp64_achieved / fp64_peak, "fp64_inst_per_update": fp64_inst,
+                "fp64_inst_source": prof.get("fp64_inst_source", "SASS count of the r01 kernel"),
+                "peak_source": f"{n_sms} SMs x 64 FP64 lanes x {sm_mhz:.0f} MHz (scripts/fp64_peak.cu measures 0.99 of it with DADD)",
+                "hbm_model_achieved": achieved, "hbm_model_peak": peak, "hbm_model_unit": "GB/s", "hbm_model_frac": achieved / peak,
+                "hbm_model_peak_source": peak_src, "algorithmic_bytes_per_update": BYTES_PER_UPDATE,
+                "traffic": per_n.get("dram_bytes_per_launch"), "traffic_source": per_n.get("source"),
+                "updates_per_launch": upd_per_launch, "launch_ms": mean_sweep_ms, "kernel_updates_per_s": kernel_rate,
                 "fp64_gflops_algorithmic": upd_per_launch * FP64_OPS_PER_UPDATE / (mean_sweep_ms * 1e-3) / 1e9,
                 "sweep_share_of_step": mean_sweep_ms * G * a.steps / (dt * 1e3)}
-    sm_mhz = (clocks or {}).get("sm_mhz") or 1965.0
-    roofline["fp64_pipe_frac"] = (roofline["kernel_updates_per_s"] / 32.0 * FP64_INST_PER_UPDATE /
-                                  torch.cuda.get_device_properties(local).multi_processor_count /
-                                  (FP64_WARP_INST_PER_CLK_SM * sm_mhz * 1e6))
-    roofline["fp64_pipe_note"] = "the binding roof (DESIGN.md 3.3): FP64-pipe warp-instructions issued / (2 per clk per SM x SM clock)"
-    prof = os.path.join(ROOT, "profiles", "sweep_traffic.json")
-    if os.path.exists(prof):
-        try:
-            roofline["traffic"] = json.load(open(prof)).get("dram_bytes_per_launch")
-        except Exception:
-            pass
     cpu = None
     if not a.no_cpu_baseline and world == 1:
         T = host_threads()
         # bounded sample: 4 sweeps of group 0 at 128^3 = 4.3e9 updates, 10-15 s of work on 16 host threads
-        v, sec, desc = run_reference_sample(a.cpu_n, G, 1, 0, T, mode="A", sweeps=4)
+        v, sec, desc = run_reference_sample(a.cpu_n, G, 1, 1, T, mode="A", sweeps=4)
         if v is not None:
             cpu = {"value": v, "unit": UNIT, "cores": T, "kind": "reference", "sample": desc}
         else:
@@ -349,8 +410,8 @@ def main():
     out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
            "ms_per_step": dt / a.steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
            "data": "synthetic", "config": config, "grind_ns": 1e9 / value, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
-           "gpu_launches": int(launches), "clocks": clocks, "wall_ms_per_step": wall / a.steps * 1e3,
-           "tile": "8x%dx%d%s" % (ctx.info(abi.INFO_TILE_Y), ctx.info(abi.INFO_TILE_Z), "" if a.tile else " (auto)"), "sweep_variant": int(ctx.info(abi.INFO_SWEEP_VARIANT)),
+           "gpu_launches": int(launches), "clocks": clocks, "parity": parity, "wall_ms_per_step": wall / a.steps * 1e3,
+           "tile": "8x%dx%d%s" % (ctx.info(abi.INFO_TILE_Y), ctx.info(abi.INFO_TILE_Z), "" if a.tile else " (auto)"), "sweep_variant": {abi.SWEEP_FLAGS: "flags", abi.SWEEP_LL: "ll"}[int(ctx.info(abi.INFO_SWEEP_VARIANT))] + ("" if a.variant != "auto" else " (auto)"),
            "units_per_rank": int(ctx.info(abi.INFO_N_UNITS)),
            "inner_loop": "doma_b200_source_iteration (library-owned)" if fused else "separate ABI calls"}
     if a.emulate_world > 1:

@@ -26,6 +26,7 @@ SCHEME_DD, SCHEME_TWDD = 0, 1
 STEP_NONE, STEP_INSERT, STEP_REMOVE, STEP_BOTH = -1, 0, 1, 2
 MAT_HAS_SRC, MAT_HAS_CHI_P, MAT_HAS_NU_SIGMA_F = 1, 2, 4
 ARR_PHI_TOT, ARR_PHI_PREV, ARR_PHI_LAST, ARR_DNP_CUR, ARR_DNP_LAST, ARR_Q, ARR_PHI_CUR = range(7)
+SWEEP_AUTO, SWEEP_FLAGS, SWEEP_LL = 0, 1, 2
 (INFO_KERNEL_LAUNCHES, INFO_SWEEP_VARIANT, INFO_N_CELLS, INFO_N_ORD, INFO_FACE_BYTES, INFO_DEVICE_BYTES, INFO_N_UNITS, INFO_N_TILES,
  INFO_TILE_Y, INFO_TILE_Z) = range(10)
 
@@ -197,6 +198,8 @@ class Library:
     _OPTIONAL = {
         "device_ptr": [C.c_void_p, C.c_int32, C.c_int32, C.POINTER(C.c_void_p)],
         "set_sweep_variant": [C.c_void_p, C.c_int32],
+        "set_pairing": [C.c_void_p, C.c_int32],
+        "set_check": [C.c_void_p, C.c_int32],
         "last_sweep_ms": [C.c_void_p, C.POINTER(C.c_float)],
         "set_threads": [C.c_void_p, C.c_int32],
         "sweep_from_host": [C.c_void_p, C.c_int32, _pd, _pd],
@@ -380,7 +383,12 @@ class Context:
         self._call("get_info", what, C.byref(out))
         return out.value
 
-    def set_sweep_variant(self, v: int): self._call("set_sweep_variant", int(v))
+    def set_sweep_variant(self, v: int):
+        """SWEEP_AUTO / SWEEP_FLAGS / SWEEP_LL: how tile-boundary faces are handed over (include/doma_b200.h)."""
+        self._call("set_sweep_variant", int(v))
+
+    def set_pairing(self, on: bool): self._call("set_pairing", int(bool(on)))
+    def set_check(self, on: bool): self._call("set_check", int(bool(on)))
     def set_tile(self, tx: int, ty: int, tz: int): self._call("set_tile", int(tx), int(ty), int(tz))
 
     def last_sweep_ms(self) -> float:

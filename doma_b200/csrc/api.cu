@@ -4,6 +4,7 @@
 
 #include <dlfcn.h>
 #include <math.h>
+#include <nvtx3/nvToolsExt.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -52,19 +53,15 @@ free_dev(T *& p)
 }
 } // namespace
 
-// Regroup this context's ordinates into sweep units: per octant, ceil(count/(32 V)) units of
-// near-equal size, each split over V batches of <= 32 lanes; lanes beyond a batch are padded with a
-// harmless direction and weight 0.  Also (re)allocates the face planes and the tile table.
+// Regroup this context's ordinates into sweep units: per octant, ceil(count/32) units of near-equal size; lanes
+// beyond a unit's ordinates are padded with a harmless direction and weight 0.  Also (re)allocates the face planes
+// and rebuilds the tile table.  The new buffers are allocated first and the context is only changed once
+// everything has succeeded, so a failure (out of memory) leaves the previous decomposition usable.
 int
-doma_build_units(doma_b200_ctx * c, int V)
+doma_build_units(doma_b200_ctx * c)
 {
-  if (V != 1)
-  {
-    snprintf(c->err, DOMA_MAX_ERR, "sweep variant: %d ordinates per lane not supported (only 1)", V);
-    return 4;
-  }
   DOMA_CUDA(c, cudaStreamSynchronize(c->stream));
-  const int L = DOMA_LANES * V;
+  const int L = DOMA_LANES;
   std::vector<int> uo;
   std::vector<double> mu, eta, xi, w;
   std::vector<SweepUnit> units;
@@ -94,7 +91,7 @@ doma_build_units(doma_b200_ctx * c, int V)
   };
   // <= 16 ordinates per octant (the shipped assembly cases): two octants that differ only in the x direction share a
   // warp, 16 lanes each (sweep.cu, PAIR) - otherwise every warp would run half empty
-  const bool paired = V == 1 && most > 0 && most <= DOMA_LANES / 2 && !getenv("DOMA_B200_NO_PAIR");
+  const bool paired = c->pairing_enabled && most > 0 && most <= DOMA_LANES / 2;
   if (paired)
   {
     for (int oct = 0; oct < 4; ++oct) // bit 2 clear: x ascending; its partner is oct | 4
@@ -124,83 +121,64 @@ doma_build_units(doma_b200_ctx * c, int V)
         const int sz = cnt / nb + (b < cnt % nb ? 1 : 0);
         units.push_back(SweepUnit{oct, sz});
         uo.push_back(oct);
-        for (int v = 0; v < V; ++v)
-        {
-          const int vsz = sz / V + (v < sz % V ? 1 : 0);
-          for (int l = 0; l < DOMA_LANES; ++l)
-            push_lane(l < vsz ? idx[pos + l] : -1);
-          pos += vsz;
-        }
+        for (int l = 0; l < DOMA_LANES; ++l)
+          push_lane(l < sz ? idx[pos + l] : -1);
+        pos += sz;
       }
     }
-  c->units_paired = paired;
-  c->device_bytes -= c->face_bytes;
-  free_dev(c->unit_octant), free_dev(c->u_mu), free_dev(c->u_eta), free_dev(c->u_xi), free_dev(c->u_w);
-  free_dev(c->face_x), free_dev(c->face_y), free_dev(c->face_z);
-  free(c->h_units);
-  c->V = V;
-  c->n_units = (int)units.size();
-  c->h_units = (SweepUnit *)malloc(sizeof(SweepUnit) * (units.size() + 1));
-  memcpy(c->h_units, units.data(), sizeof(SweepUnit) * units.size());
-  int rc = 0;
-  if ((rc = upload(c, &c->unit_octant, uo.data(), uo.size())) || (rc = upload(c, &c->u_mu, mu.data(), mu.size())) ||
-      (rc = upload(c, &c->u_eta, eta.data(), eta.size())) || (rc = upload(c, &c->u_xi, xi.data(), xi.size())) ||
-      (rc = upload(c, &c->u_w, w.data(), w.size())))
+  // ---- new device buffers (nothing of the context is touched until all of them exist) ----
+  const size_t U = units.size();
+  int * d_uo = nullptr;
+  double *d_mu = nullptr, *d_eta = nullptr, *d_xi = nullptr, *d_w = nullptr, *fx = nullptr, *fy = nullptr, *fz = nullptr;
+  const int64_t bytes_before = c->device_bytes;
+  // a face slot is 16 bytes: the LL protocol stores {low half, tag, high half, tag}; the flag protocol uses the first 8
+  const size_t slot = 2;
+  const size_t nfx = U * c->nz * c->ny * L * slot, nfy = U * c->nz * c->nx * L * slot, nfz = c->dims == 3 ? U * c->ny * c->nx * L * slot : 0;
+  auto fail = [&](int rc) {
+    free_dev(d_uo), free_dev(d_mu), free_dev(d_eta), free_dev(d_xi), free_dev(d_w), free_dev(fx), free_dev(fy), free_dev(fz);
+    c->device_bytes = bytes_before;
     return rc;
-  // face planes per unit, angle fastest
-  const size_t U = c->n_units;
-  c->face_bytes = 0;
+  };
+  int rc = 0;
+  if ((rc = upload(c, &d_uo, uo.data(), uo.size())) || (rc = upload(c, &d_mu, mu.data(), mu.size())) ||
+      (rc = upload(c, &d_eta, eta.data(), eta.size())) || (rc = upload(c, &d_xi, xi.data(), xi.size())) ||
+      (rc = upload(c, &d_w, w.data(), w.size())))
+    return fail(rc);
   if (U)
   {
-    const size_t nfx = U * c->nz * c->ny * L, nfy = U * c->nz * c->nx * L, nfz = c->dims == 3 ? U * c->ny * c->nx * L : 0;
-    DOMA_CUDA(c, cudaMalloc(&c->face_x, sizeof(double) * nfx));
-    DOMA_CUDA(c, cudaMalloc(&c->face_y, sizeof(double) * nfy));
-    if (nfz)
-      DOMA_CUDA(c, cudaMalloc(&c->face_z, sizeof(double) * nfz));
-    c->face_bytes = sizeof(double) * (nfx + nfy + nfz);
-    c->device_bytes += c->face_bytes;
-  }
-  if (c->tile_y > 0 && c->tile_z > 0)
-    return doma_sweep_setup_tiles(c, c->tile_y, c->dims == 3 ? c->tile_z : 1); // keep a tile the caller chose
-  // Default tile: the largest of 8x4x8, 8x4x4, 8x4x2, 8x2x2 (2D: 8x4, 8x2, 8x1) that still keeps every resident
-  // warp busy.  A big tile amortises the per-task cost (flag polls, fence, face rows) but a sweep unit only
-  // exposes n_tiles / n_hyperplanes independent tiles on average; with few units per GPU (angle sharding over
-  // 4-8 ranks, or 16 ordinates per octant) the wavefront starves.  Measured on B200 at 256^3 (profiles/
-  // r01_sweep_experiments.txt): 16 and 8 units -> 8x4x8, 4 units -> 8x4x4, 2 units -> 8x4x2.
-  static const int cand3[][2] = {{4, 8}, {4, 4}, {4, 2}, {2, 2}, {4, 1}, {2, 1}};
-  static const int cand2[][2] = {{4, 1}, {2, 1}, {1, 1}};
-  const int(*cand)[2] = c->dims == 3 ? cand3 : cand2;
-  const int n_cand = c->dims == 3 ? 6 : 3;
-  // resident warps are 16 per SM (4 CTAs x 4 warps); the measured optimum sits at 1.0-1.8 tasks in flight per
-  // resident warp (2 units: 8x4x4 0.70 -> 7.53 ms, 8x4x2 1.00 -> 7.02 ms, 8x2x2 1.55 -> 7.61 ms), hence 15 not 16
-  const double want = 15.0 * c->n_sms;
-  // When no tile saturates the GPU (the shipped assembly and 2D cases) the sweep is a chain of task latencies,
-  // and the tile that minimises  hyperplanes x L + tasks x L / resident warps  wins, with the measured single-warp
-  // task latency L = cells x 0.195 us + 3.4 us (profiles/r01_task_latency.txt).  Measured: the 2D transient case
-  // 8x1 422 us, 8x2 299 us, 8x4 256 us per sweep (profiles/r01_small_case_tiles.txt).
-  int pick = -1, best = 0;
-  double best_cost = 0.0;
-  for (int i = 0; i < n_cand; ++i)
-  {
-    const double ntx = (c->nx + 7) / 8, nty = (c->ny + cand[i][0] - 1) / cand[i][0], ntz = (c->nz + cand[i][1] - 1) / cand[i][1];
-    const double units = c->n_units > 0 ? c->n_units : 1;
-    const double planes = ntx + nty + ntz - 2.0;
-    const double in_flight = units * ntx * nty * ntz / planes;
-    if (in_flight >= want)
+    cudaError_t e = cudaMalloc(&fx, sizeof(double) * nfx);
+    if (e == cudaSuccess)
+      e = cudaMalloc(&fy, sizeof(double) * nfy);
+    if (e == cudaSuccess && nfz)
+      e = cudaMalloc(&fz, sizeof(double) * nfz);
+    if (e == cudaSuccess)
+      e = cudaMemset(fx, 0, sizeof(double) * nfx);
+    if (e == cudaSuccess)
+      e = cudaMemset(fy, 0, sizeof(double) * nfy);
+    if (e == cudaSuccess && nfz)
+      e = cudaMemset(fz, 0, sizeof(double) * nfz);
+    if (e != cudaSuccess)
     {
-      pick = i;
-      break;
+      snprintf(c->err, DOMA_MAX_ERR, "build_units: face planes (%zu bytes): %s", sizeof(double) * (nfx + nfy + nfz), cudaGetErrorString(e));
+      return fail(100 + (int)e);
     }
-    const double L = 8.0 * cand[i][0] * cand[i][1] * 0.195 + 3.4;
-    const double cost = planes * L + units * ntx * nty * ntz * L / (16.0 * c->n_sms);
-    if (i == 0 || cost < best_cost)
-      best = i, best_cost = cost;
   }
-  if (pick < 0)
-    pick = best;
-  rc = doma_sweep_setup_tiles(c, cand[pick][0], cand[pick][1]);
-  c->tile_auto = true;
-  return rc;
+  // ---- commit ----
+  free_dev(c->unit_octant), free_dev(c->u_mu), free_dev(c->u_eta), free_dev(c->u_xi), free_dev(c->u_w);
+  free_dev(c->face_x), free_dev(c->face_y), free_dev(c->face_z);
+  c->device_bytes = bytes_before - c->face_bytes + (int64_t)(sizeof(double) * (nfx + nfy + nfz));
+  c->face_bytes = (int64_t)(sizeof(double) * (nfx + nfy + nfz));
+  c->unit_octant = d_uo, c->u_mu = d_mu, c->u_eta = d_eta, c->u_xi = d_xi, c->u_w = d_w;
+  c->face_x = fx, c->face_y = fy, c->face_z = fz;
+  c->units_paired = paired;
+  free(c->h_units);
+  c->n_units = (int)U;
+  c->h_units = (SweepUnit *)malloc(sizeof(SweepUnit) * (U + 1));
+  memcpy(c->h_units, units.data(), sizeof(SweepUnit) * U);
+  c->ll_epoch = 0; // the planes are zero again: LL tags restart
+  if (!c->tile_auto && c->tile_y > 0 && c->tile_z > 0)
+    return doma_sweep_setup_tiles(c, c->tile_y, c->dims == 3 ? c->tile_z : 1); // keep a tile the caller chose
+  return doma_choose_tile(c);
 }
 
 namespace
@@ -226,6 +204,12 @@ create_impl(doma_b200_ctx * c, const doma_b200_problem * p)
   c->G = p->n_groups, c->M = p->n_mat, c->D = p->n_delayed_max > 0 ? p->n_delayed_max : 0;
   c->n_ord = p->n_ord;
   c->scheme = p->scheme, c->mode = p->mode, c->dt = p->dt;
+  c->pairing_enabled = true;
+  c->variant = DOMA_SWEEP_AUTO;
+  {
+    const char * chk = getenv("DOMA_B200_CHECK"); // documented in include/doma_b200.h (doma_b200_set_check)
+    c->check = chk && *chk && *chk != '0';
+  }
   DOMA_CUDA(c, cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
   c->own_stream = true;
   DOMA_CUDA(c, cudaEventCreate(&c->ev0));
@@ -319,7 +303,8 @@ create_impl(doma_b200_ctx * c, const doma_b200_problem * p)
     }
     (void)per_oct;
     DOMA_CUDA(c, cudaMalloc(&c->work_counter, sizeof(int)));
-    if ((rc = doma_build_units(c, 1)))
+    c->tile_auto = true;
+    if ((rc = doma_build_units(c)))
       return rc;
   }
   DOMA_CUDA(c, cudaMalloc(&c->red_partial, sizeof(double) * 2 * 1184));
@@ -379,10 +364,39 @@ extern "C" {
 int
 doma_b200_create(const doma_b200_problem * p, doma_b200_ctx ** out)
 {
-  if (!p || !out || (p->dims != 2 && p->dims != 3) || p->nx < 1 || p->ny < 1 || (p->dims == 3 && p->nz < 1) || p->n_groups < 1 ||
-      p->n_mat < 1 || p->n_ord < 0 || !p->dx || !p->dy || !p->mat_of_cell || !p->sigma_t || !p->sigma_s)
+  // every pointer the create path dereferences is checked here: a bad caller gets rc != 0 and a message, not a fault
+  const char * missing = nullptr;
+  if (!p || !out)
+    missing = "problem / out pointer";
+  else if (p->dims != 2 && p->dims != 3)
+    missing = "dims (2 or 3)";
+  else if (p->nx < 1 || p->ny < 1 || (p->dims == 3 && p->nz < 1))
+    missing = "nx, ny, nz (>= 1)";
+  else if (p->n_groups < 1 || p->n_mat < 1 || p->n_ord < 0 || p->n_delayed_max < 0)
+    missing = "n_groups, n_mat (>= 1), n_ord, n_delayed_max (>= 0)";
+  else if ((int64_t)p->n_mat * p->n_groups * p->n_groups > INT32_MAX || (int64_t)p->n_mat * p->n_groups * (p->n_delayed_max + 1) > INT32_MAX)
+    missing = "n_mat * n_groups^2 and n_mat * n_groups * n_delayed_max (must fit 31 bits)";
+  else if (!p->dx || !p->dy || (p->dims == 3 && !p->dz))
+    missing = "dx, dy, dz";
+  else if (!p->mat_of_cell || !p->mat_flags || !p->n_delayed)
+    missing = "mat_of_cell, mat_flags, n_delayed";
+  else if (!p->sigma_t || !p->sigma_s || !p->nu_sigma_f || !p->chi_p || !p->src || !p->inv_v)
+    missing = "sigma_t, sigma_s, nu_sigma_f, chi_p, src, inv_v (zeros when a material has none)";
+  else if (p->n_delayed_max > 0 && (!p->chi_d || !p->beta || !p->lambda))
+    missing = "chi_d, beta, lambda (n_delayed_max > 0)";
+  else if (p->step_type && (!p->step_t_insert || !p->step_t_remove || !p->step_src))
+    missing = "step_t_insert, step_t_remove, step_src (step_type given)";
+  else if (p->n_ord > 0 && (!p->ord_octant || !p->mu || !p->eta || !p->xi || !p->w))
+    missing = "ord_octant, mu, eta, xi, w (n_ord > 0)";
+  else if (p->scheme != DOMA_SCHEME_DD && p->scheme != DOMA_SCHEME_TWDD)
+    missing = "scheme (DOMA_SCHEME_DD or DOMA_SCHEME_TWDD)";
+  else if (p->mode != DOMA_MODE_FIXED && p->mode != DOMA_MODE_EIGEN && p->mode != DOMA_MODE_TRANSIENT)
+    missing = "mode (DOMA_MODE_*)";
+  if (missing)
   {
-    snprintf(g_create_err, DOMA_MAX_ERR, "create: invalid problem description");
+    snprintf(g_create_err, DOMA_MAX_ERR, "create: invalid problem description: %s", missing);
+    if (out)
+      *out = nullptr;
     return 1;
   }
   doma_b200_ctx * c = (doma_b200_ctx *)calloc(1, sizeof(doma_b200_ctx));
@@ -481,9 +495,16 @@ doma_b200_synchronize(doma_b200_ctx * c)
   return 0;
 }
 
+// every entry point: null check, device selection, one NVTX range named after the ABI call (visible in nsys / ncu)
+struct NvtxRange
+{
+  explicit NvtxRange(const char * name) { nvtxRangePushA(name); }
+  ~NvtxRange() { nvtxRangePop(); }
+};
 #define ENTER(c)                    \
   if (!(c))                         \
     return 1;                       \
+  NvtxRange nvtx_range_(__func__);  \
   DOMA_CUDA(c, cudaSetDevice((c)->device))
 #define CHECK_GROUP(c, g)                                                             \
   if ((g) < 0 || (g) >= (c)->G)                                                       \
@@ -786,7 +807,7 @@ doma_b200_get_info(doma_b200_ctx * c, int32_t what, int64_t * out)
   switch (what)
   {
     case DOMA_INFO_KERNEL_LAUNCHES: *out = c->launches; break;
-    case DOMA_INFO_SWEEP_VARIANT: *out = c->V; break;
+    case DOMA_INFO_SWEEP_VARIANT: *out = doma_sweep_uses_ll(c) ? DOMA_SWEEP_LL : DOMA_SWEEP_FLAGS; break;
     case DOMA_INFO_N_CELLS: *out = c->N; break;
     case DOMA_INFO_N_ORD: *out = c->n_ord; break;
     case DOMA_INFO_FACE_BYTES: *out = c->face_bytes; break;
@@ -804,14 +825,31 @@ int
 doma_b200_set_sweep_variant(doma_b200_ctx * c, int32_t variant)
 {
   ENTER(c);
-  if (variant != 1)
+  if (variant != DOMA_SWEEP_AUTO && variant != DOMA_SWEEP_FLAGS && variant != DOMA_SWEEP_LL)
   {
-    snprintf(c->err, DOMA_MAX_ERR, "set_sweep_variant: only variant 1 (persistent KBA tiles, one ordinate per lane) exists");
+    snprintf(c->err, DOMA_MAX_ERR, "set_sweep_variant: %d is none of DOMA_SWEEP_AUTO, DOMA_SWEEP_FLAGS, DOMA_SWEEP_LL", variant);
     return 4;
   }
-  if (variant == c->V)
+  c->variant = variant;
+  return c->tile_auto ? doma_choose_tile(c) : 0; // the best tile depends on the protocol
+}
+
+int
+doma_b200_set_pairing(doma_b200_ctx * c, int32_t on)
+{
+  ENTER(c);
+  if ((on != 0) == c->pairing_enabled)
     return 0;
-  return doma_build_units(c, variant);
+  c->pairing_enabled = on != 0;
+  return doma_build_units(c);
+}
+
+int
+doma_b200_set_check(doma_b200_ctx * c, int32_t on)
+{
+  ENTER(c);
+  c->check = on != 0;
+  return 0;
 }
 
 int
@@ -823,6 +861,8 @@ doma_b200_set_tile(doma_b200_ctx * c, int32_t tx, int32_t ty, int32_t tz)
     snprintf(c->err, DOMA_MAX_ERR, "set_tile: the x extent of a tile is fixed to 8 (row held in registers)");
     return 6;
   }
+  if (ty == 0 && tz == 0)
+    return doma_choose_tile(c); // back to the library's own choice
   return doma_sweep_setup_tiles(c, ty, tz);
 }
 

@@ -23,7 +23,7 @@
 struct SweepUnit
 {
   int octant;  // DOMA_OCT_*
-  int n_lanes; // ordinates in this unit, <= 32 V
+  int n_lanes; // ordinates in this unit, <= 32
 };
 
 struct doma_b200_ctx
@@ -52,19 +52,24 @@ struct doma_b200_ctx
   // into sweep units (octant x V batches of <=32 ordinates), lane-major
   int32_t * h_ord_octant;
   double *h_mu, *h_eta, *h_xi, *h_w; // [n_ord] signed, as passed in
-  int V;               // ordinates per lane: 1, or 2 when octants hold more than 32 ordinates (3D)
   int n_units;
   SweepUnit * h_units; // host copy
   int * unit_octant;   // [U]
   bool units_paired;   // every unit carries two octants that differ in x, 16 lanes each (sweep.cu, PAIR)
-  double *u_mu, *u_eta, *u_xi, *u_w; // [U][V][32] absolute direction cosines; padding lanes: 1,1,1,w=0
+  bool pairing_enabled; // doma_b200_set_pairing (default on)
+  bool check;           // doma_b200_set_check / DOMA_B200_CHECK=1
+  double *u_mu, *u_eta, *u_xi, *u_w; // [U][32] absolute direction cosines; padding lanes: 1,1,1,w=0
 
   // sweep scratch
   int tile_x, tile_y, tile_z; // tile_x is fixed to 8 by the kernel (row held in registers)
-  bool tile_auto;             // tile chosen by the library's occupancy heuristic (api.cu), not by set_tile
+  bool tile_auto;             // tile (and protocol) chosen by doma_choose_tile (sweep.cu), not by set_tile
+  int variant;                // DOMA_SWEEP_AUTO / _FLAGS / _LL as requested (doma_b200_set_sweep_variant)
+  bool use_ll;                // doma_choose_tile's protocol choice when variant is AUTO
+  bool last_sweep_ll;         // protocol of the most recent sweep
+  int ll_epoch;               // LL tag epoch (20 bits; the planes are cleared when it wraps)
   int ntx, nty, ntz, n_tiles;
   uint32_t * tile_order; // [n_tiles] packed (I',J',K') sorted by I'+J'+K'
-  double *face_x, *face_y, *face_z; // [U][nz][ny][32V], [U][nz][nx][32V], [U][ny][nx][32V]
+  double *face_x, *face_y, *face_z; // [U][nz][ny][32], [U][nz][nx][32], [U][ny][nx][32]
   int * tile_done;                   // [U][n_tiles] epoch of completion
   int * work_counter;                // [1]
   int epoch;
@@ -124,9 +129,12 @@ int doma_launch_mg_residual(doma_b200_ctx * c);
 int doma_launch_k_sums(doma_b200_ctx * c, double k);
 int doma_launch_sig_eff(doma_b200_ctx * c, int g);
 
-// api.cu: (re)build sweep units, face planes and the tile table for V ordinates per lane
-int doma_build_units(doma_b200_ctx * c, int V);
+// api.cu: (re)build sweep units, face planes and the tile table
+int doma_build_units(doma_b200_ctx * c);
 
 // sweep.cu
 int doma_sweep_setup_tiles(doma_b200_ctx * c, int ty, int tz);
+int doma_choose_tile(doma_b200_ctx * c);
+bool doma_sweep_uses_ll(const doma_b200_ctx * c);
 int doma_launch_sweep(doma_b200_ctx * c, int g);
+int doma_sweep_check(doma_b200_ctx * c); // check mode: every tile done, phi_cur finite (synchronises)

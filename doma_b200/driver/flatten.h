@@ -10,6 +10,7 @@
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 #include <map>
 #include <string>
 #include <unordered_map>
@@ -42,7 +43,8 @@ struct FlatProblem
   int dims = 3, scheme = DOMA_SCHEME_TWDD, mode = DOMA_MODE_FIXED, device = 0;
   double dt = 0.0;
   std::vector<double> dx, dy, dz;
-  std::vector<int32_t> mat_of_cell;
+  std::vector<unsigned int> block_of_cell; // XML block id per cell, x fastest (what CartesianCell::_block_id holds)
+  std::vector<int32_t> mat_of_cell;        // dense material index per cell (mapMaterials)
   int G = 1, M = 0, D = 0;
   std::vector<unsigned int> block_of_mat;
   std::vector<int32_t> mat_flags, n_delayed, step_type;
@@ -50,11 +52,68 @@ struct FlatProblem
   std::vector<int32_t> ord_octant;
   std::vector<double> mu, eta, xi, w;
 
+  // Flat builder: per-cell widths and block ids straight from the parsed input, without constructing
+  // the reference's per-cell objects.  Same arithmetic as the mesh constructors (src/BrickMesh3D.cpp:44-81,
+  // src/BrickMesh2D.cpp:38-63): every interval i contributes n_i cells of width d_i / n_i (n_i already carries the
+  // refinement factor, src/InputParameters.cpp:212-214), and the block id of interval (i,j,k) is repeated over its cells.
+  // --check-flat compares the result, bit for bit, with what the mesh built.
+  void setGeometryFromParams(const InputParameters & p)
+  {
+    dims = static_cast<int>(p._num_dims);
+    auto widths = [](const std::vector<double> & d, const std::vector<unsigned int> & n, std::vector<double> & out) {
+      out.clear();
+      for (std::size_t i = 0; i < n.size(); ++i)
+        out.insert(out.end(), n[i], d[i] / static_cast<double>(n[i]));
+    };
+    widths(p._dx, p._x_intervals, dx);
+    widths(p._dy, p._y_intervals, dy);
+    const std::vector<unsigned int> one(1, 1u);
+    const std::vector<unsigned int> & nzv = dims == 3 ? p._z_intervals : one;
+    if (dims == 3)
+      widths(p._dz, p._z_intervals, dz);
+    else
+      dz.clear();
+    const std::size_t bx = p._x_intervals.size(), by = p._y_intervals.size();
+    if (bx * by * nzv.size() != p._blocks.size())
+    {
+      std::fprintf(stderr, "Error: The blocks vector is not equal to the number of subdivisions!\n");
+      std::exit(1);
+    }
+    block_of_cell.clear();
+    block_of_cell.reserve(dx.size() * dy.size() * (dims == 3 ? dz.size() : 1));
+    std::vector<unsigned int> row;
+    for (std::size_t k = 0; k < nzv.size(); ++k)
+      for (unsigned int kk = 0; kk < nzv[k]; ++kk)
+        for (std::size_t j = 0; j < by; ++j)
+        {
+          row.clear();
+          for (std::size_t i = 0; i < bx; ++i)
+            row.insert(row.end(), p._x_intervals[i], p._blocks[(k * by + j) * bx + i]);
+          for (unsigned int jj = 0; jj < p._y_intervals[j]; ++jj)
+            block_of_cell.insert(block_of_cell.end(), row.begin(), row.end());
+        }
+  }
+
+  // block ids -> dense material indices (after setMaterials)
+  void mapMaterials()
+  {
+    mat_of_cell.resize(block_of_cell.size());
+    unsigned int last_block = 0;
+    int last_index = -1;
+    for (std::size_t c = 0; c < block_of_cell.size(); ++c)
+    {
+      if (last_index < 0 || block_of_cell[c] != last_block)
+        last_block = block_of_cell[c], last_index = materialIndex(last_block);
+      mat_of_cell[c] = last_index;
+    }
+  }
+
   // materials: dense index = rank of the block id (the reference keys an unordered_map by block id)
   void setMaterials(const std::unordered_map<unsigned int, MaterialProps> & mats,
                     const std::unordered_map<unsigned int, SourceStep> & steps, unsigned int groups)
   {
     G = static_cast<int>(groups);
+    block_of_mat.clear();
     std::map<unsigned int, const MaterialProps *> sorted;
     for (const auto & kv : mats)
       sorted[kv.first] = &kv.second;
@@ -122,6 +181,7 @@ struct FlatProblem
   // i % world == rank, a unit being a batch of <= 32 ordinates of one octant (as api.cu build_units)
   void setQuadrature(const GCAngularQuadrature & quad, const RankInfo & r)
   {
+    ord_octant.clear(), mu.clear(), eta.clear(), xi.clear(), w.clear();
     int unit = 0;
     for (unsigned int o = 0u; o < 8u; ++o)
     {
@@ -175,14 +235,20 @@ struct DriverConfig
   RankInfo rank;
   int tile_y = 0, tile_z = 0; // 0 = library default
   double last_k = 1.0;                // TransportSolver::_k after the last updateEigenvalue
+  double solve_seconds = 0.0;         // wall time of the solve*() call alone
   doma_b200_ctx * live_ctx = nullptr; // context of the solver currently alive (owned by its operator)
+  FlatProblem flat;                   // what the context was created from (kept for the dumps)
   // --fast-dump: steady / eigenvalue runs write their final text dump through doma_b200_dump_text instead of
   // BrickMesh::dumpToTextFile (same bytes, tests/test_text_output.py), and computeMGFluxResidual no longer copies
-  // the flux into the per-cell host vectors after every outer iteration.  The geometry kept for the static files:
+  // the flux into the per-cell host vectors after every outer iteration.
   bool fast_dump = false;
-  int geom_dims = 3, geom_groups = 1;
-  std::vector<double> geom_dx, geom_dy, geom_dz;
-  std::vector<unsigned int> geom_block_of_cell;
+  // flat mesh (--flat, automatic above 2 M cells in steady / eigenvalue runs): geometry and block ids come from
+  // FlatProblem::setGeometryFromParams, the solver is handed a stub mesh of one cell per block; implies --fast-dump
+  bool flat_mesh = false;
+  bool check_flat = false;   // --check-flat: compare the flat builder with the mesh the reference built, then exit
+  bool separate_si = false;  // --separate-si: the reference's own three-call source iteration instead of doma_b200_source_iteration
+  bool poison = false;       // --check: DOMA_B200_CHECK-style poisoning of the sweep scratch (doma_b200_set_check)
+  std::string raw_dir;       // --dump-raw <dir>: final state as raw doubles, full precision
 };
 inline DriverConfig & config()
 {
@@ -190,12 +256,35 @@ inline DriverConfig & config()
   return c;
 }
 
+inline void
+check(int rc, doma_b200_ctx * ctx, const char * what)
+{
+  if (rc != 0)
+  {
+    // the reference's fatal-error style: print and exit(1) (src/BrickMesh3D.cpp:26-30)
+    std::fprintf(stderr, "Error: %s failed (%d): %s\n", what, rc, doma_b200_last_error(ctx));
+    std::exit(1);
+  }
+}
+
+inline std::FILE *
+openOrDie(const std::string & path, const char * mode)
+{
+  std::FILE * f = std::fopen(path.c_str(), mode);
+  if (!f)
+  {
+    std::fprintf(stderr, "Error: cannot open %s\n", path.c_str());
+    std::exit(1);
+  }
+  return f;
+}
+
 // <base>_dims.txt, _blocks.txt, _meshx/y/z.txt exactly as BrickMesh3D::dumpToTextFile writes them
 // (src/BrickMesh3D.cpp:216-258; 2D: src/BrickMesh2D.cpp:169-205), from the flattened geometry.
 inline void
-writeGeometryFiles(const DriverConfig & c, const std::string & base)
+writeGeometryFiles(const FlatProblem & fp, int groups, const std::string & base)
 {
-  const std::size_t nx = c.geom_dx.size(), ny = c.geom_dy.size(), nz = c.geom_dims == 3 ? c.geom_dz.size() : 1;
+  const std::size_t nx = fp.dx.size(), ny = fp.dy.size(), nz = fp.dims == 3 ? fp.dz.size() : 1;
   auto centres = [](const std::vector<double> & w) { // the reference's running centre (src/BrickMesh3D.cpp:84-101)
     std::vector<double> v(w.size());
     double acc = 0.5 * w[0];
@@ -206,19 +295,19 @@ writeGeometryFiles(const DriverConfig & c, const std::string & base)
     }
     return v;
   };
-  const auto xc = centres(c.geom_dx), yc = centres(c.geom_dy), zc = c.geom_dims == 3 ? centres(c.geom_dz) : std::vector<double>();
-  std::FILE * f = std::fopen((base + "_dims.txt").c_str(), "w");
+  const auto xc = centres(fp.dx), yc = centres(fp.dy), zc = fp.dims == 3 ? centres(fp.dz) : std::vector<double>();
+  std::FILE * f = openOrDie(base + "_dims.txt", "w");
   std::fprintf(f, "num_x: %zu\nnum_y: %zu\n", nx, ny);
-  if (c.geom_dims == 3)
+  if (fp.dims == 3)
     std::fprintf(f, "num_z: %zu\n", nz);
-  std::fprintf(f, "num_g: %d\n", c.geom_groups);
+  std::fprintf(f, "num_g: %d\n", groups);
   std::fclose(f);
-  f = std::fopen((base + "_blocks.txt").c_str(), "w");
-  for (unsigned int b : c.geom_block_of_cell)
+  f = openOrDie(base + "_blocks.txt", "w");
+  for (unsigned int b : fp.block_of_cell)
     std::fprintf(f, "%u\n", b);
   std::fclose(f);
   std::vector<double> v(nx * ny * nz);
-  for (int axis = 0; axis < c.geom_dims; ++axis)
+  for (int axis = 0; axis < fp.dims; ++axis)
   {
     for (std::size_t k = 0, n = 0; k < nz; ++k)
       for (std::size_t j = 0; j < ny; ++j)
@@ -233,17 +322,73 @@ writeGeometryFiles(const DriverConfig & c, const std::string & base)
   }
 }
 
-// NCCL unique-id exchange between the ranks of one box through a file (rank 0 writes, others poll).
+// --check-flat: 0 when the flat builder reproduced the mesh's widths and block ids bit for bit
+inline int
+reportFlatCheck(const FlatProblem & flat, const FlatProblem & mesh)
+{
+  auto same = [](const std::vector<double> & a, const std::vector<double> & b) {
+    return a.size() == b.size() && (a.empty() || std::memcmp(a.data(), b.data(), a.size() * sizeof(double)) == 0);
+  };
+  const bool ok = same(flat.dx, mesh.dx) && same(flat.dy, mesh.dy) && same(flat.dz, mesh.dz) && flat.block_of_cell == mesh.block_of_cell;
+  std::printf("FLATCHECK %s nx=%zu ny=%zu nz=%zu cells=%zu\n", ok ? "identical" : "DIFFERENT", flat.dx.size(), flat.dy.size(),
+              flat.dz.size(), flat.block_of_cell.size());
+  return ok ? 0 : 4;
+}
+
+// NCCL unique-id exchange between the ranks of one launch (main.cpp).
 void bootstrapComm(doma_b200_ctx * ctx, const RankInfo & r);
 
-inline void
-check(int rc, doma_b200_ctx * ctx, const char * what)
+inline doma_b200_ctx *
+createContext(const FlatProblem & flat)
 {
+  const auto p = flat.view();
+  doma_b200_ctx * ctx = nullptr;
+  const int rc = doma_b200_create(&p, &ctx);
   if (rc != 0)
   {
-    // the reference's fatal-error style: print and exit(1) (src/BrickMesh3D.cpp:26-30)
-    std::fprintf(stderr, "Error: %s failed (%d): %s\n", what, rc, doma_b200_last_error(ctx));
+    std::fprintf(stderr, "Error: doma_b200_create failed (%d): %s\n", rc, doma_b200_last_error(nullptr));
     std::exit(1);
   }
+  auto & cf = config();
+  if (cf.tile_y > 0 && cf.tile_z > 0)
+    check(doma_b200_set_tile(ctx, 8, cf.tile_y, cf.tile_z), ctx, "doma_b200_set_tile");
+  if (cf.poison)
+    check(doma_b200_set_check(ctx, 1), ctx, "doma_b200_set_check");
+  bootstrapComm(ctx, cf.rank);
+  cf.live_ctx = ctx;
+  return ctx;
+}
+
+// --dump-raw <dir>: the final state at full precision, the files oracle/ref_harness.cpp writes for the reference
+// (phi_g<g>.f64, dnp_d<d>.f64, meta.json), so the same digests check both.
+inline void
+dumpRaw(doma_b200_ctx * ctx, const FlatProblem & fp, bool ok, const std::string & dir)
+{
+  std::vector<double> buf(fp.mat_of_cell.size());
+  auto put = [&](int which, int index, const std::string & name) {
+    check(doma_b200_get_array(ctx, which, index, buf.data()), ctx, "doma_b200_get_array");
+    if (config().rank.rank != 0)
+      return;
+    std::FILE * f = openOrDie(dir + "/" + name, "wb");
+    if (std::fwrite(buf.data(), sizeof(double), buf.size(), f) != buf.size())
+    {
+      std::fprintf(stderr, "Error: short write to %s/%s\n", dir.c_str(), name.c_str());
+      std::exit(1);
+    }
+    std::fclose(f);
+  };
+  for (int g = 0; g < fp.G; ++g)
+    put(DOMA_ARR_PHI_TOT, g, "phi_g" + std::to_string(g) + ".f64");
+  if (fp.mode == DOMA_MODE_TRANSIENT)
+    for (int d = 0; d < fp.D; ++d)
+      put(DOMA_ARR_DNP_CUR, d, "dnp_d" + std::to_string(d) + ".f64");
+  if (config().rank.rank != 0)
+    return;
+  std::FILE * f = openOrDie(dir + "/meta.json", "w");
+  std::fprintf(f, "{\"dims\": %d, \"nx\": %zu, \"ny\": %zu, \"nz\": %zu, \"groups\": %d, \"n_delayed\": %d, \"ok\": %s, \"k\": %.17g, "
+                  "\"solve_seconds\": %.6f}\n",
+               fp.dims, fp.dx.size(), fp.dy.size(), fp.dims == 3 ? fp.dz.size() : (std::size_t)1, fp.G, fp.D, ok ? "true" : "false",
+               config().last_k, config().solve_seconds);
+  std::fclose(f);
 }
 } // namespace doma_b200_driver

@@ -114,7 +114,8 @@ int doma_b200_update_scatter_source(doma_b200_ctx * ctx, int32_t g);
 /* sweep ----------------------------------------------------------------------------------------- */
 /* sweep(g) (3D:565-622, 2D:565-602): phi_cur[c] += sum over this context's ordinates of w*psi_c.
  * With ordinates sharded over ranks the caller sums phi_cur across ranks afterwards
- * (doma_b200_device_ptr(DOMA_PTR_PHI_CUR) + an all-reduce on the same stream). */
+ * (doma_b200_allreduce_phi_cur, or doma_b200_device_ptr(ctx, DOMA_ARR_PHI_CUR, 0, &p) + its own collective on
+ * the same stream); doma_b200_source_iteration does both. */
 int doma_b200_sweep(doma_b200_ctx * ctx, int32_t g);
 
 /* Host-buffer form of sweep(g), the call a host-resident driver makes: copies q (N doubles, reference
@@ -195,7 +196,7 @@ int doma_b200_device_ptr(doma_b200_ctx * ctx, int32_t which, int32_t index, void
 enum
 {
   DOMA_INFO_KERNEL_LAUNCHES = 0, /* kernels launched by this context so far */
-  DOMA_INFO_SWEEP_VARIANT = 1,   /* 1 = persistent KBA tiles, one ordinate per lane (the only variant so far) */
+  DOMA_INFO_SWEEP_VARIANT = 1,   /* face-exchange protocol of the next sweep: DOMA_SWEEP_FLAGS or DOMA_SWEEP_LL (see set_sweep_variant) */
   DOMA_INFO_N_CELLS = 2,
   DOMA_INFO_N_ORD = 3,
   DOMA_INFO_FACE_BYTES = 4,
@@ -206,8 +207,25 @@ enum
   DOMA_INFO_TILE_Z = 9
 };
 int doma_b200_get_info(doma_b200_ctx * ctx, int32_t what, int64_t * out);
-/* select the sweep implementation (see DOMA_INFO_SWEEP_VARIANT); default 1 */
+/* How the persistent sweep kernel hands tile-boundary face fluxes from the warp that produced them to the warp that
+ * consumes them (sweep.cu):
+ *   DOMA_SWEEP_FLAGS  8-byte face values + one done-flag per (unit, tile) behind a device-scope fence: least traffic,
+ *                     best when the wavefront saturates the GPU (many units per GPU);
+ *   DOMA_SWEEP_LL     16-byte self-validating face values (two 8-byte {half, tag} words, no flag, no fence): a consumer
+ *                     follows its producer row by row instead of tile by tile; best when the sweep is a chain of task
+ *                     latencies (few units per GPU: 8-way angle sharding, the shipped assembly and 2D cases);
+ *   DOMA_SWEEP_AUTO   (default) the library picks per problem from units x tiles per hyperplane vs resident warps.
+ * Results are identical (same arithmetic, same order); only the timing differs. */
+enum { DOMA_SWEEP_AUTO = 0, DOMA_SWEEP_FLAGS = 1, DOMA_SWEEP_LL = 2 };
 int doma_b200_set_sweep_variant(doma_b200_ctx * ctx, int32_t variant);
+/* Octant pairing: with <= 16 ordinates per octant two octants that differ only in the x direction share a warp,
+ * 16 lanes each (default on; off = one octant per warp, for A/B tests).  Rebuilds the sweep units. */
+int doma_b200_set_pairing(doma_b200_ctx * ctx, int32_t on);
+/* Debug mode (also enabled by the environment variable DOMA_B200_CHECK=1 at create): before every sweep the face planes
+ * are poisoned (NaN / an impossible tag) and after it the library verifies that every tile of every unit completed and
+ * that phi_cur is finite; a missed wavefront dependency then fails the call (error 30) instead of reading last
+ * sweep's value.  Costs a synchronisation per sweep. */
+int doma_b200_set_check(doma_b200_ctx * ctx, int32_t on);
 /* KBA tile extents in cells; tx must be 8 (the row a warp keeps in registers), ty <= 4. Rebuilds the tile table.
  * Without this call the library picks the tile from the mesh size and the number of sweep units (api.cu). */
 int doma_b200_set_tile(doma_b200_ctx * ctx, int32_t tx, int32_t ty, int32_t tz);

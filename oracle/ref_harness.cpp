@@ -22,6 +22,7 @@
 #include <cstring>
 #include <filesystem>
 #include <fstream>
+#include <functional>
 #include <iomanip>
 #include <iostream>
 #include <limits>
@@ -57,6 +58,41 @@ struct RunResult
 };
 
 std::string g_scratch = "/tmp";
+// --snapshots: the state after every outer iteration (power iteration / multigroup iteration) of a long run.
+// The reference prints "Performing PI <n>" / "Performing MGI <n>" at the top of each outer (src/TransportSolver3D.cpp:41,276);
+// when the line for n >= 1 goes by, its state is exactly the state after n complete outers, i.e. what a run with
+// mg_max_it = n ends with.  A filtering streambuf on std::cout sees the line and calls g_snapshot(n): the reference's
+// loop is neither edited nor restated, and a run that is stopped early still leaves usable full-precision fixtures.
+std::function<void(unsigned int)> g_snapshot;
+
+class SnapshotBuf : public std::streambuf
+{
+public:
+  explicit SnapshotBuf(std::streambuf * sink) : _sink(sink) {}
+
+protected:
+  int_type overflow(int_type ch) override
+  {
+    if (ch == traits_type::eof())
+      return traits_type::not_eof(ch);
+    const char c = static_cast<char>(ch);
+    if (c == '\n')
+    {
+      unsigned int n = 0u;
+      if (g_snapshot && (std::sscanf(_line.c_str(), "Performing PI %u", &n) == 1 || std::sscanf(_line.c_str(), "Performing MGI %u", &n) == 1) && n >= 1u)
+        g_snapshot(n);
+      _line.clear();
+    }
+    else if (_line.size() < 64u)
+      _line.push_back(c);
+    return _sink->sputc(c);
+  }
+  int sync() override { return _sink->pubsync(); }
+
+private:
+  std::streambuf * _sink;
+  std::string _line;
+};
 std::string g_text_base; // --text <base>: let the reference write its own text dumps there (fixtures for the output path)
 
 template <typename Solver>
@@ -145,6 +181,27 @@ dumpState(Mesh & mesh, unsigned int groups, bool three_d, const std::string & ou
   (void)three_d;
 }
 
+template <typename Mesh, typename Solver>
+void
+installSnapshots(Mesh & mesh, Solver & solver, unsigned int groups, const std::string & out)
+{
+  g_snapshot = [&mesh, &solver, groups, out](unsigned int n_outer)
+  {
+    const std::string dir = out + "/snap_" + std::to_string(n_outer);
+    std::filesystem::create_directories(dir);
+    const auto n = mesh._cells.size();
+    std::vector<double> phi(n);
+    for (unsigned int g = 0u; g < groups; ++g)
+    {
+      for (std::size_t i = 0; i < n; ++i)
+        phi[i] = mesh._cells[i]._total_scalar_flux[g];
+      dumpRaw(dir + "/phi_g" + std::to_string(g) + ".f64", phi);
+    }
+    std::ofstream f(dir + "/meta.json");
+    f << std::setprecision(17) << "{\"outer\": " << n_outer << ", \"k\": " << solver._k << ", \"k_prev\": " << solver._k_prev << "}\n";
+  };
+}
+
 void
 writeMeta(const std::string & out, unsigned int dims, unsigned int nx, unsigned int ny, unsigned int nz,
           unsigned int groups, unsigned int n_ord, const RunResult & r, int threads, double mesh_seconds)
@@ -163,24 +220,29 @@ main(int argc, char ** argv)
 {
   if (argc < 4)
   {
-    std::cerr << "usage: ref_harness <case.xml> <threads> <out_dir> [--no-dump] [--text <file base>]\n";
+    std::cerr << "usage: ref_harness <case.xml> <threads> <out_dir> [--no-dump] [--text <file base>] [--snapshots]\n";
     return 2;
   }
   const std::string xml = argv[1];
   const int threads = std::max(1, std::atoi(argv[2]));
   const std::string out = argv[3];
-  bool dump = true;
+  bool dump = true, snapshots = false;
   for (int i = 4; i < argc; ++i)
   {
     if (std::string(argv[i]) == "--no-dump")
       dump = false;
     else if (std::string(argv[i]) == "--text" && i + 1 < argc)
       g_text_base = argv[++i];
+    else if (std::string(argv[i]) == "--snapshots")
+      snapshots = true;
   }
   std::filesystem::create_directories(out);
   g_scratch = out + "/scratch";
   std::filesystem::create_directories(g_scratch);
 
+  SnapshotBuf snap_buf(std::cout.rdbuf());
+  if (snapshots)
+    std::cout.rdbuf(&snap_buf);
   std::cout << std::setprecision(17);
   const auto params = parseInputParameters(xml);
   omp_set_num_threads(threads);
@@ -198,6 +260,7 @@ main(int argc, char ** argv)
     if (params._eq_type == EquationType::DD)
     {
       DDTransportSolver3D solver(mesh, params, true, threads);
+      if (snapshots) installSnapshots(mesh, solver, params._num_e_groups, out);
       r = runSolver(solver, params._mode);
       n_ord = solver._angular_quad.totalOrder();
       if (dump) dumpQuad(solver, out);
@@ -205,6 +268,7 @@ main(int argc, char ** argv)
     else
     {
       TWDDTransportSolver3D solver(mesh, params, true, threads);
+      if (snapshots) installSnapshots(mesh, solver, params._num_e_groups, out);
       r = runSolver(solver, params._mode);
       n_ord = solver._angular_quad.totalOrder();
       if (dump) dumpQuad(solver, out);
@@ -231,6 +295,7 @@ main(int argc, char ** argv)
     if (params._eq_type == EquationType::DD)
     {
       DDTransportSolver2D solver(mesh, params, true, threads);
+      if (snapshots) installSnapshots(mesh, solver, params._num_e_groups, out);
       r = runSolver(solver, params._mode);
       n_ord = solver._angular_quad.totalOrder() / 2u;
       if (dump) dumpQuad(solver, out);
@@ -238,6 +303,7 @@ main(int argc, char ** argv)
     else
     {
       TWDDTransportSolver2D solver(mesh, params, true, threads);
+      if (snapshots) installSnapshots(mesh, solver, params._num_e_groups, out);
       r = runSolver(solver, params._mode);
       n_ord = solver._angular_quad.totalOrder() / 2u;
       if (dump) dumpQuad(solver, out);
@@ -251,6 +317,7 @@ main(int argc, char ** argv)
     std::cerr << "ref_harness: only 2D and 3D cases are on the hot path\n";
     return 2;
   }
+  g_snapshot = nullptr;
   std::cout << "HARNESS ok=" << (r.ok ? 1 : 0) << " solve_seconds=" << r.seconds << " threads=" << threads << std::endl;
   return 0;
 }

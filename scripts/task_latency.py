@@ -9,11 +9,14 @@ import numpy as np
 from doma_b200 import abi
 from doma_b200.synthetic import random_problem
 
+VARIANT = {"flags": abi.SWEEP_FLAGS, "ll": abi.SWEEP_LL}[sys.argv[1] if len(sys.argv) > 1 else "flags"]
+
 def chain_ms(ty, tz, n_tiles, full_lanes=True):
     prob = random_problem((8, ty, tz * n_tiles), G=1, npol=4, nazi=4, seed=3, void=False)
     keep = np.nonzero(prob.ord_octant == 0)[0][:32 if full_lanes else 8]
     prob = prob.with_ordinates(keep)
     ctx = abi.Context(prob)
+    ctx.set_sweep_variant(VARIANT)
     ctx.set_tile(8, ty, tz)
     ctx.reset_state(0.0)
     ctx.set_array(abi.ARR_Q, 0, np.ones(prob.n_cells))
@@ -25,6 +28,7 @@ def chain_ms(ty, tz, n_tiles, full_lanes=True):
 if __name__ == "__main__":
     n = 120
     res = {}
+    print("protocol", sys.argv[1] if len(sys.argv) > 1 else "flags")
     for ty, tz in [(4, 2), (4, 8), (4, 32), (2, 2), (4, 1)]:
         ms, u = chain_ms(ty, tz, n)
         res[(ty, tz)] = ms / n * 1e3

@@ -127,3 +127,22 @@ def test_solver_loop_matches_reference_trace_strings(oracle_lib):
     assert s.solve() is False          # mg_max_it reached -> "PI failed to converge"
     assert any(l.startswith("PI failed to converge after 3 iterations") for l in lines)
     assert np.array_equal(np.array(s.trace.k_history), np.append(g["k_history"], s.k)[: len(s.trace.k_history)])
+
+
+def test_create_rejects_missing_pointers_with_a_message():
+    """Every pointer the create path dereferences is validated first: rc != 0 and a message naming the field, not a fault
+    across the C ABI (no GPU needed: validation precedes device selection)."""
+    import ctypes as C
+
+    lib = abi.load_library()
+    for field, word in [("dz", "dz"), ("mu", "ord_octant"), ("nu_sigma_f", "nu_sigma_f"), ("mat_flags", "mat_flags"), ("step_src", "step_src")]:
+        prob = random_problem((4, 3, 2))
+        cp = prob.as_c()
+        setattr(cp, field, C.cast(None, type(getattr(cp, field))))
+        h = C.c_void_p()
+        rc = lib.fn["create"](C.byref(cp), C.byref(h))
+        assert rc == 1 and not h.value
+        assert word in lib.last_error(None), lib.last_error(None)
+    cp = random_problem((4, 3, 2)).as_c()
+    cp.scheme = 7
+    assert lib.fn["create"](C.byref(cp), C.byref(C.c_void_p())) == 1 and "scheme" in lib.last_error(None)

@@ -67,3 +67,80 @@ def test_driver_fast_dump_writes_the_reference_files(name, tmp_path):
             ref = {m.name[len("ref"):]: tar.extractfile(m).read() for m in tar.getmembers()}
         assert sorted(ref) == sorted(fast)
         assert not [n for n in ref if ref[n] != fast[n]]
+
+
+# ---- the drop-in at FULL size: the reference's own loops + libdoma_b200.so against the reference's digests ----
+FULL_CASES = ["k1", "asm_fs_3outer", "asm_eig_3pi", "tr2d_1step", "syn256_b"]
+
+
+@pytest.mark.parametrize("name", FULL_CASES)
+def test_driver_full_size_matches_reference_digest(name, tmp_path):
+    """doma_b200_driver --dump-raw on the shipped cases at their shipped size (and on bench.py's 256^3 workload, which
+    takes the flat mesh builder automatically): flux within 1e-10, k within 1e-9, identical iteration traces."""
+    import json
+
+    from doma_b200.digest import K_TOL, SYNTHETIC_FLOOR, flux_errors, within_bounds
+
+    if not os.path.exists(DRIVER):
+        pytest.fail("doma_b200/bin/doma_b200_driver missing: build() compiles it where /root/reference exists")
+    g = np.load(os.path.join(ROOT, "tests", "golden", "full", name + ".npz"))
+    xml = tmp_path / (name + ".xml")
+    xml.write_text(open(golden_case_path("full_" + name)).read())
+    raw = tmp_path / "raw"
+    r = subprocess.run([DRIVER, "-i", str(xml), "--no-output" if not name.startswith("tr2d") else "--fast-dump", "--dump-raw", str(raw)],
+                       capture_output=True, text=True, timeout=1800, cwd=tmp_path)
+    assert "DRIVER impl=b200" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+    tail = r.stdout.rsplit("DRIVER", 1)[1]
+    assert ("ok=1" in tail) == bool(g["ok"])
+    if name.startswith("syn"):
+        assert "flat_mesh=1" in tail          # 16.8 M cells: geometry straight from the parsed input
+    si = [int(x) for x in re.findall(r"SI (?:converged|failed to converge) after (\d+) iterations", r.stdout)]
+    assert si == list(g["si_counts"]), "source-iteration trace differs from the reference"
+    meta = json.load(open(raw / "meta.json"))
+    G, dims = meta["groups"], meta["dims"]
+    phi = np.stack([np.fromfile(raw / f"phi_g{i}.f64") for i in range(G)])
+    errs = flux_errors(phi, g, dims, SYNTHETIC_FLOOR if name.startswith("syn") else 0.0)
+    assert within_bounds(errs), errs
+    if "eig" in name:
+        assert abs(meta["k"] - float(g["k"])) <= K_TOL
+    if name.startswith("tr2d"):
+        dnp = np.stack([np.fromfile(raw / f"dnp_d{i}.f64") for i in range(meta["n_delayed"])])
+        e = np.abs(dnp[:, g["idx"]] - g["dnp_s"]) / np.maximum(np.abs(g["dnp_s"]), 1e-300)
+        assert float(e.max()) <= 1e-10
+
+
+def test_driver_separate_si_and_check_mode(tmp_path):
+    """--separate-si (the reference's own three-call source iteration) and --check (poisoned sweep scratch) give the trace
+    of the default fused path."""
+    name = "asm_eig_small_1sweep"
+    outs = []
+    for flags in ([], ["--separate-si"], ["--check"]):
+        xml = tmp_path / (name + ".xml")
+        xml.write_text(open(golden_case_path(name)).read())
+        r = subprocess.run([DRIVER, "-i", str(xml), "--no-output", "--verbose"] + flags, capture_output=True, text=True, timeout=600)
+        assert "DRIVER impl=b200" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+        outs.append([l for l in r.stdout.splitlines() if l.startswith(("Performing", "SI ", "PI ", "k ="))])
+    assert outs[0] == outs[1] == outs[2] and len(outs[0]) > 6
+
+
+def test_driver_two_ranks(tmp_path):
+    """Two ranks, one GPU each: the NCCL id travels over TCP (no files), the flux is summed over ranks inside
+    doma_b200_source_iteration; same trace and k as the single-rank golden run."""
+    import torch
+
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs (run with gpurun --gpus 2)")
+    name = "asm_eig_small_1sweep"
+    g = load_golden(name)
+    xml = tmp_path / (name + ".xml")
+    xml.write_text(open(golden_case_path(name)).read())
+    procs = []
+    for rank in range(2):
+        env = dict(os.environ, RANK=str(rank), WORLD_SIZE="2", LOCAL_RANK=str(rank), MASTER_ADDR="127.0.0.1", MASTER_PORT="29533")
+        procs.append(subprocess.Popen([DRIVER, "-i", str(xml), "--no-output"], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, env=env))
+    outs = [p.communicate(timeout=600) for p in procs]
+    assert all(p.returncode in (0, 3) for p in procs), outs
+    tail = outs[0][0].rsplit("DRIVER", 1)[1]
+    assert abs(float(re.search(r" k=([-0-9.e+]+)", tail).group(1)) - float(g["k"])) <= 1e-9
+    si = [int(x) for x in re.findall(r"SI (?:converged|failed to converge) after (\d+) iterations", outs[0][0])]
+    assert si == list(g["si_counts"])

@@ -16,6 +16,7 @@ from conftest import GOLDEN, golden_case_path
 
 import doma_b200 as d
 from doma_b200 import abi
+from doma_b200.digest import flux_errors, within_bounds
 
 FULL = os.path.join(GOLDEN, "full")
 NAMES = sorted(f[:-4] for f in os.listdir(FULL) if f.endswith(".npz"))
@@ -57,6 +58,8 @@ def check_against_digest(name, lib, fused_si=False):
     slabs = phi.reshape(G, nz, ny * nx).sum(axis=2) if prob.dims == 3 else phi.reshape(G, ny, nx).sum(axis=2)
     # (a slab's sum is compared relative to the largest slab of its group: far slabs are sums of the +- fluxes above)
     np.testing.assert_allclose(slabs, g["slab_sum"], rtol=1e-10, atol=10 * floor * float(np.abs(g["slab_sum"]).max()))
+    errs = flux_errors(phi, g, prob.dims, floor)      # the same comparison bench.py prints as "parity" at every rank count
+    assert within_bounds(errs), errs
     if params.mode == abi.MODE_EIGEN:
         assert abs(s.k - float(g["k"])) <= K_TOL
         n = min(len(s.trace.k_history), len(g["k_history"]))   # the reference prints k only for iterations it continues from
