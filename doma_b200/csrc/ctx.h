@@ -67,6 +67,7 @@ struct doma_b200_ctx
   bool use_ll;                // doma_choose_tile's protocol choice when variant is AUTO
   bool last_sweep_ll;         // protocol of the most recent sweep
   int ll_epoch;               // LL tag epoch (20 bits; the planes are cleared when it wraps)
+  bool planes_raw;            // the face planes were last written by a FLAGS sweep (raw doubles, no tags)
   int ntx, nty, ntz, n_tiles;
   uint32_t * tile_order; // [n_tiles] packed (I',J',K') sorted by I'+J'+K'
   double *face_x, *face_y, *face_z; // [U][nz][ny][32], [U][nz][nx][32], [U][ny][nx][32]
