@@ -174,6 +174,8 @@ def main():
                          "driver's sequence) instead of doma_b200_source_iteration")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cell-sharding", action="store_true",
+                    help="N > 1: the r01 scheme (all-reduce of phi_cur, elementwise phases replicated on every rank)")
     ap.add_argument("--no-parity", action="store_true", help="skip the comparison with the reference digest after the first warm-up step")
     a = ap.parse_args()
     a.warmup = max(a.warmup, 3) if a.impl == "b200" else max(a.warmup, 1)
@@ -248,6 +250,8 @@ def main():
         ty, tz = [int(v) for v in a.tile.lower().split("x")]
         ctx.set_tile(8, ty, tz)
     allreduce = make_allreduce(ctx) if world > 1 else None
+    if world > 1 and a.no_cell_sharding:
+        ctx.set_cell_sharding(False)
     N = prob.n_cells
     updates_per_step = float(N) * full_ord * G
 
@@ -346,7 +350,7 @@ def main():
                 ctx.update_scatter_source(g)
             r = ctx.mg_residual()
             ctx.host_wait()
-            return r + float(pn[G - 1][0])
+            return r + float(pn[G - 1][ctx.info(abi.INFO_CELL_LO)])
 
         for _ in range(2):
             e2e_step()
@@ -361,8 +365,11 @@ def main():
             t = torch.tensor([de], dtype=torch.float64, device="cuda")
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             de = float(t.item())
-        e2e = {"value": updates_per_step * a.steps / de, "unit": UNIT, "h2d_bytes_per_step": 8 * N * G,
-               "d2h_bytes_per_step": 8 * N * G, "ms_per_step": de / a.steps * 1e3,
+        # bytes over PCIe per step, all ranks together: cell-sharded ranks move their own cells only (1x the arrays);
+        # replicated ranks each move whole arrays (world x)
+        copies = 1 if (world == 1 or not a.no_cell_sharding) else world
+        e2e = {"value": updates_per_step * a.steps / de, "unit": UNIT, "h2d_bytes_per_step": 8 * N * G * copies,
+               "d2h_bytes_per_step": 8 * N * G * copies, "ms_per_step": de / a.steps * 1e3,
                "api": "doma_b200_stage_q_from_host + doma_b200_sweep_from_host_async + doma_b200_host_wait (C ABI, pinned host buffers, copies overlapped with the neighbouring groups' kernels) per group + the step's source/residual calls"}
 
     if rank != 0:
@@ -413,7 +420,10 @@ def main():
            "gpu_launches": int(launches), "clocks": clocks, "parity": parity, "wall_ms_per_step": wall / a.steps * 1e3,
            "tile": "8x%dx%d%s" % (ctx.info(abi.INFO_TILE_Y), ctx.info(abi.INFO_TILE_Z), "" if a.tile else " (auto)"), "sweep_variant": {abi.SWEEP_FLAGS: "flags", abi.SWEEP_LL: "ll"}[int(ctx.info(abi.INFO_SWEEP_VARIANT))] + ("" if a.variant != "auto" else " (auto)"),
            "units_per_rank": int(ctx.info(abi.INFO_N_UNITS)),
-           "inner_loop": "doma_b200_source_iteration (library-owned)" if fused else "separate ABI calls"}
+           "inner_loop": "doma_b200_source_iteration (library-owned)" if fused else "separate ABI calls",
+           "exchange": ("none (1 GPU)" if world == 1 else
+                        "all-reduce(phi_cur), elementwise phases replicated" if a.no_cell_sharding else
+                        "all-gather(q) -> sweep -> reduce-scatter(phi_cur), elementwise phases on the rank's own cells")}
     if a.emulate_world > 1:
         out["emulated_world"] = a.emulate_world
     print(json.dumps(out))

@@ -28,7 +28,7 @@ MAT_HAS_SRC, MAT_HAS_CHI_P, MAT_HAS_NU_SIGMA_F = 1, 2, 4
 ARR_PHI_TOT, ARR_PHI_PREV, ARR_PHI_LAST, ARR_DNP_CUR, ARR_DNP_LAST, ARR_Q, ARR_PHI_CUR = range(7)
 SWEEP_AUTO, SWEEP_FLAGS, SWEEP_LL = 0, 1, 2
 (INFO_KERNEL_LAUNCHES, INFO_SWEEP_VARIANT, INFO_N_CELLS, INFO_N_ORD, INFO_FACE_BYTES, INFO_DEVICE_BYTES, INFO_N_UNITS, INFO_N_TILES,
- INFO_TILE_Y, INFO_TILE_Z) = range(10)
+ INFO_TILE_Y, INFO_TILE_Z, INFO_CELL_LO, INFO_CELL_HI) = range(12)
 
 _pd = C.POINTER(C.c_double)
 _pi = C.POINTER(C.c_int32)
@@ -213,6 +213,7 @@ class Library:
         "comm_unique_id": [C.c_char_p, C.c_int32],
         "comm_init": [C.c_void_p, C.c_int32, C.c_int32, C.c_char_p, C.c_int32],
         "allreduce_phi_cur": [C.c_void_p],
+        "set_cell_sharding": [C.c_void_p, C.c_int32],
         "set_tile": [C.c_void_p, C.c_int32, C.c_int32, C.c_int32],
         "source_iteration": [C.c_void_p, C.c_int32, C.c_double, C.c_int32, C.POINTER(C.c_int32), _pd, _pd],
     }
@@ -386,6 +387,10 @@ class Context:
     def set_sweep_variant(self, v: int):
         """SWEEP_AUTO / SWEEP_FLAGS / SWEEP_LL: how tile-boundary faces are handed over (include/doma_b200.h)."""
         self._call("set_sweep_variant", int(v))
+
+    def set_cell_sharding(self, on: bool):
+        """Multi-rank contexts: keep / drop the cell sharding of the elementwise phases (collective; see the header)."""
+        self._call("set_cell_sharding", int(bool(on)))
 
     def set_pairing(self, on: bool): self._call("set_pairing", int(bool(on)))
     def set_check(self, on: bool): self._call("set_check", int(bool(on)))

@@ -37,9 +37,10 @@ alloc_zero(doma_b200_ctx * c, double ** dst, size_t n)
 {
   *dst = nullptr;
   const size_t cnt = n ? n : 1;
-  DOMA_CUDA(c, cudaMalloc((void **)dst, sizeof(double) * cnt));
-  DOMA_CUDA(c, cudaMemset(*dst, 0, sizeof(double) * cnt));
-  c->device_bytes += sizeof(double) * cnt;
+  // DOMA_PAD doubles behind every per-cell array: the cell-sharded collectives work on nranks equal slices
+  DOMA_CUDA(c, cudaMalloc((void **)dst, sizeof(double) * (cnt + DOMA_PAD)));
+  DOMA_CUDA(c, cudaMemset(*dst, 0, sizeof(double) * (cnt + DOMA_PAD)));
+  c->device_bytes += sizeof(double) * (cnt + DOMA_PAD);
   return 0;
 }
 
@@ -321,10 +322,12 @@ struct NcclApi
   int (*GetUniqueId)(void *);
   int (*CommInitRank)(void **, int, char[128], int); // ncclUniqueId is a 128-byte struct passed by value
   int (*AllReduce)(const void *, void *, size_t, int, int, void *, cudaStream_t);
+  int (*ReduceScatter)(const void *, void *, size_t, int, int, void *, cudaStream_t);
+  int (*AllGather)(const void *, void *, size_t, int, void *, cudaStream_t);
   int (*CommDestroy)(void *);
   const char * (*GetErrorString)(int);
 };
-NcclApi g_nccl = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+NcclApi g_nccl = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 
 struct NcclId
 {
@@ -348,9 +351,11 @@ load_nccl(char * err)
   g_nccl.GetUniqueId = (int (*)(void *))dlsym(g_nccl.lib, "ncclGetUniqueId");
   g_nccl.CommInitRank = (int (*)(void **, int, char[128], int))dlsym(g_nccl.lib, "ncclCommInitRank");
   g_nccl.AllReduce = (int (*)(const void *, void *, size_t, int, int, void *, cudaStream_t))dlsym(g_nccl.lib, "ncclAllReduce");
+  g_nccl.ReduceScatter = (int (*)(const void *, void *, size_t, int, int, void *, cudaStream_t))dlsym(g_nccl.lib, "ncclReduceScatter");
+  g_nccl.AllGather = (int (*)(const void *, void *, size_t, int, void *, cudaStream_t))dlsym(g_nccl.lib, "ncclAllGather");
   g_nccl.CommDestroy = (int (*)(void *))dlsym(g_nccl.lib, "ncclCommDestroy");
   g_nccl.GetErrorString = (const char * (*)(int))dlsym(g_nccl.lib, "ncclGetErrorString");
-  if (!g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.AllReduce || !g_nccl.CommDestroy)
+  if (!g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.AllReduce || !g_nccl.ReduceScatter || !g_nccl.AllGather || !g_nccl.CommDestroy)
   {
     snprintf(err, DOMA_MAX_ERR, "comm: libnccl lacks a required symbol");
     return 21;
@@ -427,7 +432,7 @@ doma_b200_destroy(doma_b200_ctx * c)
                    c->sigma_s, c->nu_sigma_f, c->chi_p, c->src, c->inv_v, c->chi_d, c->beta, c->lambda, c->step_t_insert,
                    c->step_t_remove, c->step_src, c->sig_cell, c->phi_tot, c->phi_prev, c->phi_last, c->dnp_cur, c->dnp_last,
                    c->q, c->phi_cur, c->unit_octant, c->u_mu, c->u_eta, c->u_xi, c->u_w, c->tile_order, c->face_x, c->face_y,
-                   c->face_z, c->tile_done, c->work_counter, c->red_partial, c->red_out};
+                   c->face_z, c->tile_done, c->work_counter, c->red_partial, c->red_out, c->phi_red, c->gather_tmp};
   for (void * p : ptrs)
     if (p)
       cudaFree(p);
@@ -557,14 +562,22 @@ doma_b200_sweep_from_host(doma_b200_ctx * c, int32_t g, const double * q_host, d
 {
   ENTER(c);
   CHECK_GROUP(c, g);
-  DOMA_CUDA(c, cudaMemcpyAsync(c->q, q_host, sizeof(double) * c->N, cudaMemcpyHostToDevice, c->stream));
+  if (!q_host || !phi_cur_out)
+  {
+    snprintf(c->err, DOMA_MAX_ERR, "sweep_from_host: null host pointer");
+    return 1;
+  }
+  // cell-sharded ranks move their own cells only: 1/P of q up (then an all-gather over NVLink), 1/P of phi down
+  const int64_t lo = ew_lo(c), hi = ew_hi(c);
+  DOMA_CUDA(c, cudaMemcpyAsync(c->q + lo, q_host + lo, sizeof(double) * (hi - lo), cudaMemcpyHostToDevice, c->stream));
+  c->q_slice_only = c->cell_sharded;
   DOMA_CUDA(c, cudaMemsetAsync(c->phi_cur, 0, sizeof(double) * c->N, c->stream));
   int rc = doma_launch_sweep(c, g);
   if (rc)
     return rc;
   if (c->nccl_comm && (rc = doma_b200_allreduce_phi_cur(c)))
     return rc;
-  DOMA_CUDA(c, cudaMemcpyAsync(phi_cur_out, c->phi_cur, sizeof(double) * c->N, cudaMemcpyDeviceToHost, c->stream));
+  DOMA_CUDA(c, cudaMemcpyAsync(phi_cur_out + lo, ew_phi_cur(c) + lo, sizeof(double) * (hi - lo), cudaMemcpyDeviceToHost, c->stream));
   DOMA_CUDA(c, cudaStreamSynchronize(c->stream));
   return 0;
 }
@@ -615,7 +628,8 @@ doma_b200_stage_q_from_host(doma_b200_ctx * c, const double * q_host)
   if (rc)
     return rc;
   DOMA_CUDA(c, cudaStreamWaitEvent(c->copy_in, c->ev_q_consumed, 0)); // the previous staged source has left q_stage
-  DOMA_CUDA(c, cudaMemcpyAsync(c->q_stage, q_host, sizeof(double) * c->N, cudaMemcpyHostToDevice, c->copy_in));
+  DOMA_CUDA(c, cudaMemcpyAsync(c->q_stage + ew_lo(c), q_host + ew_lo(c), sizeof(double) * (ew_hi(c) - ew_lo(c)), cudaMemcpyHostToDevice,
+                               c->copy_in)); // cell-sharded: the own cells only; the sweep all-gathers q over NVLink
   DOMA_CUDA(c, cudaEventRecord(c->ev_q_staged, c->copy_in));
   c->q_is_staged = true;
   return 0;
@@ -648,7 +662,8 @@ doma_b200_sweep_from_host_async(doma_b200_ctx * c, int32_t g, const double * q_h
     return rc;
   DOMA_CUDA(c, cudaEventRecord(c->ev_snap, c->stream));
   DOMA_CUDA(c, cudaStreamWaitEvent(c->copy_out, c->ev_snap, 0));
-  DOMA_CUDA(c, cudaMemcpyAsync(phi_cur_out, c->phi_snap, sizeof(double) * c->N, cudaMemcpyDeviceToHost, c->copy_out));
+  DOMA_CUDA(c, cudaMemcpyAsync(phi_cur_out + ew_lo(c), c->phi_snap + ew_lo(c), sizeof(double) * (ew_hi(c) - ew_lo(c)),
+                               cudaMemcpyDeviceToHost, c->copy_out)); // cell-sharded: the summed increment of the own cells
   DOMA_CUDA(c, cudaEventRecord(c->ev_copied, c->copy_out));
   c->copy_pending = true;
   return 0;
@@ -754,6 +769,41 @@ array_ptr(doma_b200_ctx * c, int which, int index)
   }
 }
 
+namespace
+{
+// cell-sharded: the slices of one per-cell array on all ranks -> gather_tmp (a collective: every rank calls it)
+int
+gather_slices(doma_b200_ctx * c, const double * array)
+{
+  const int r = g_nccl.AllGather(array + c->cell_lo, c->gather_tmp, (size_t)c->slice, /*ncclDouble*/ 8, c->nccl_comm, c->stream);
+  if (r)
+  {
+    snprintf(c->err, DOMA_MAX_ERR, "ncclAllGather: %s", g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "?");
+    return 24;
+  }
+  c->launches += 1;
+  return 0;
+}
+
+// the device address a whole per-cell array can be copied to the host from (cell-sharded: after a gather)
+int
+whole_array(doma_b200_ctx * c, int which, const double * p, const double ** out)
+{
+  *out = p;
+  if (!c->cell_sharded || which == DOMA_ARR_Q)
+    return which == DOMA_ARR_Q ? doma_comm_gather_q(c) : 0;
+  if (which == DOMA_ARR_PHI_CUR)
+  {
+    if (!c->phi_cur_reduced)
+      return 0; // between a sweep and its reduction: this rank's partial sums
+    p = c->phi_red - c->cell_lo;
+  }
+  const int rc = gather_slices(c, p);
+  *out = c->gather_tmp;
+  return rc;
+}
+} // namespace
+
 int
 doma_b200_get_array(doma_b200_ctx * c, int32_t which, int32_t index, double * host_out)
 {
@@ -764,6 +814,9 @@ doma_b200_get_array(doma_b200_ctx * c, int32_t which, int32_t index, double * ho
     snprintf(c->err, DOMA_MAX_ERR, "get_array: no array %d[%d] in this context", which, index);
     return 4;
   }
+  const int rc = whole_array(c, which, p, &p);
+  if (rc)
+    return rc;
   DOMA_CUDA(c, cudaMemcpyAsync(host_out, p, sizeof(double) * c->N, cudaMemcpyDeviceToHost, c->stream));
   DOMA_CUDA(c, cudaStreamSynchronize(c->stream));
   return 0;
@@ -779,7 +832,17 @@ doma_b200_set_array(doma_b200_ctx * c, int32_t which, int32_t index, const doubl
     snprintf(c->err, DOMA_MAX_ERR, "set_array: no array %d[%d] in this context", which, index);
     return 4;
   }
-  DOMA_CUDA(c, cudaMemcpyAsync(p, host_in, sizeof(double) * c->N, cudaMemcpyHostToDevice, c->stream));
+  if (c->cell_sharded && which == DOMA_ARR_PHI_CUR)
+  {
+    // the increment the residual / update kernels read = the summed one of the own cells; the local accumulator restarts
+    DOMA_CUDA(c, cudaMemcpyAsync(c->phi_red, host_in + c->cell_lo, sizeof(double) * (c->cell_hi - c->cell_lo), cudaMemcpyHostToDevice, c->stream));
+    DOMA_CUDA(c, cudaMemsetAsync(c->phi_cur, 0, sizeof(double) * c->N, c->stream));
+    c->phi_cur_reduced = true;
+  }
+  else
+    DOMA_CUDA(c, cudaMemcpyAsync(p, host_in, sizeof(double) * c->N, cudaMemcpyHostToDevice, c->stream));
+  if (which == DOMA_ARR_Q)
+    c->q_slice_only = false;
   DOMA_CUDA(c, cudaStreamSynchronize(c->stream));
   return 0;
 }
@@ -816,6 +879,8 @@ doma_b200_get_info(doma_b200_ctx * c, int32_t what, int64_t * out)
     case DOMA_INFO_N_TILES: *out = c->n_tiles; break;
     case DOMA_INFO_TILE_Y: *out = c->tile_y; break;
     case DOMA_INFO_TILE_Z: *out = c->tile_z; break;
+    case DOMA_INFO_CELL_LO: *out = ew_lo(c); break;
+    case DOMA_INFO_CELL_HI: *out = ew_hi(c); break;
     default: snprintf(c->err, DOMA_MAX_ERR, "get_info: unknown item %d", what); return 4;
   }
   return 0;
@@ -953,6 +1018,8 @@ struct DumpJob
   char err[DOMA_MAX_ERR] = {0};
   void run()
   {
+    if (base.empty()) // a rank that only takes part in the gather of a cell-sharded run
+      flux.clear(), dnps.clear();
     for (size_t g = 0; g < flux.size() && !rc; ++g)
       rc = write_values_text(flux[g].data(), N, (base + "_g" + std::to_string(g) + "_flux.txt").c_str(), n_threads, err);
     for (size_t d = 0; d < dnps.size() && !rc; ++d)
@@ -989,7 +1056,12 @@ snapshot_for_dump(doma_b200_ctx * c, DumpJob * j, const char * file_base, int wi
   for (int g = 0; g < c->G; ++g)
   {
     j->flux[g].resize(N);
-    DOMA_CUDA(c, cudaMemcpy(j->flux[g].data(), c->phi_tot + (size_t)g * N, sizeof(double) * N, cudaMemcpyDeviceToHost));
+    const double * src = nullptr;
+    const int rc = whole_array(c, DOMA_ARR_PHI_TOT, c->phi_tot + (size_t)g * N, &src);
+    if (rc)
+      return rc;
+    DOMA_CUDA(c, cudaMemcpyAsync(j->flux[g].data(), src, sizeof(double) * N, cudaMemcpyDeviceToHost, c->stream));
+    DOMA_CUDA(c, cudaStreamSynchronize(c->stream));
   }
   if (with_dnps && c->D > 0 && c->dnp_cur)
   {
@@ -1005,7 +1077,12 @@ snapshot_for_dump(doma_b200_ctx * c, DumpJob * j, const char * file_base, int wi
     for (int d = 0; d < dmax; ++d)
     {
       j->dnps[d].resize(N);
-      DOMA_CUDA(c, cudaMemcpy(j->dnps[d].data(), c->dnp_cur + (size_t)d * N, sizeof(double) * N, cudaMemcpyDeviceToHost));
+      const double * src = nullptr;
+      const int rc = whole_array(c, DOMA_ARR_DNP_CUR, c->dnp_cur + (size_t)d * N, &src);
+      if (rc)
+        return rc;
+      DOMA_CUDA(c, cudaMemcpyAsync(j->dnps[d].data(), src, sizeof(double) * N, cudaMemcpyDeviceToHost, c->stream));
+      DOMA_CUDA(c, cudaStreamSynchronize(c->stream));
       for (size_t i = 0; i < N; ++i)
         if (nd[mat[i]] != dmax)
           j->dnps[d][i] = 0.0;
@@ -1106,19 +1183,114 @@ doma_b200_comm_init(doma_b200_ctx * c, int32_t rank, int32_t nranks, const char 
   }
   c->rank = rank;
   c->nranks = nranks;
+  return nranks > 1 ? doma_b200_set_cell_sharding(c, 1) : 0;
+}
+
+// Cell sharding of everything that is not the sweep (ctx.h): on by default once a communicator of more than one rank
+// exists; off = the r01 scheme (all-reduce of phi_cur, every rank repeats the elementwise work on all cells).
+// Must be switched on all ranks alike, between solves (the state of the other cells is not moved).
+int
+doma_b200_set_cell_sharding(doma_b200_ctx * c, int32_t on)
+{
+  ENTER(c);
+  if (!c->nccl_comm || c->nranks < 2)
+  {
+    if (on)
+    {
+      snprintf(c->err, DOMA_MAX_ERR, "set_cell_sharding: needs a communicator of at least two ranks (doma_b200_comm_init)");
+      return 4;
+    }
+    return 0;
+  }
+  DOMA_CUDA(c, cudaStreamSynchronize(c->stream));
+  if (!on)
+  {
+    if (c->cell_sharded)
+    {
+      // every array becomes whole on every rank again
+      const int64_t GN = (int64_t)c->G * c->N;
+      (void)GN;
+      double * arrays[] = {c->phi_tot, c->phi_prev, c->phi_last};
+      for (double * base : arrays)
+        for (int g = 0; base && g < c->G; ++g)
+        {
+          int rc = gather_slices(c, base + (size_t)g * c->N);
+          if (rc)
+            return rc;
+          DOMA_CUDA(c, cudaMemcpyAsync(base + (size_t)g * c->N, c->gather_tmp, sizeof(double) * c->N, cudaMemcpyDeviceToDevice, c->stream));
+        }
+      double * dn[] = {c->dnp_cur, c->dnp_last};
+      for (double * base : dn)
+        for (int d = 0; base && d < c->D; ++d)
+        {
+          int rc = gather_slices(c, base + (size_t)d * c->N);
+          if (rc)
+            return rc;
+          DOMA_CUDA(c, cudaMemcpyAsync(base + (size_t)d * c->N, c->gather_tmp, sizeof(double) * c->N, cudaMemcpyDeviceToDevice, c->stream));
+        }
+      int rc = doma_comm_gather_q(c);
+      if (rc)
+        return rc;
+      if (c->phi_cur_reduced)
+      {
+        if ((rc = gather_slices(c, c->phi_red - c->cell_lo)))
+          return rc;
+        DOMA_CUDA(c, cudaMemcpyAsync(c->phi_cur, c->gather_tmp, sizeof(double) * c->N, cudaMemcpyDeviceToDevice, c->stream));
+      }
+      DOMA_CUDA(c, cudaStreamSynchronize(c->stream));
+    }
+    c->cell_sharded = false;
+    return 0;
+  }
+  if (c->cell_sharded)
+    return 0;
+  const int64_t P = c->nranks;
+  c->slice = (((c->N + P - 1) / P) + 1) & ~(int64_t)1; // even: 16-byte aligned slices
+  if (P * c->slice > c->N + DOMA_PAD)
+  {
+    snprintf(c->err, DOMA_MAX_ERR, "set_cell_sharding: %lld ranks need more padding than the %d doubles the arrays carry", (long long)P, DOMA_PAD);
+    return 4;
+  }
+  c->cell_lo = std::min<int64_t>(c->N, c->rank * c->slice);
+  c->cell_hi = std::min<int64_t>(c->N, c->cell_lo + c->slice);
+  if (!c->phi_red)
+  {
+    DOMA_CUDA(c, cudaMalloc(&c->phi_red, sizeof(double) * c->slice));
+    DOMA_CUDA(c, cudaMalloc(&c->gather_tmp, sizeof(double) * P * c->slice));
+    c->device_bytes += sizeof(double) * (P + 1) * c->slice;
+  }
+  // the increment of the own cells as it stands (phi_cur is whole and identical on every rank at this point)
+  DOMA_CUDA(c, cudaMemcpyAsync(c->phi_red, c->phi_cur + c->cell_lo, sizeof(double) * (c->cell_hi - c->cell_lo), cudaMemcpyDeviceToDevice, c->stream));
+  DOMA_CUDA(c, cudaMemsetAsync(c->phi_cur, 0, sizeof(double) * c->N, c->stream));
+  DOMA_CUDA(c, cudaStreamSynchronize(c->stream));
+  c->cell_sharded = true;
+  c->q_slice_only = false;
+  c->phi_cur_reduced = true;
   return 0;
 }
 
+// The sum of the sweep's increment over the ranks, on the context's stream.  Replicated mode: one in-place
+// ncclAllReduce(phi_cur).  Cell-sharded mode: ncclReduceScatter(phi_cur) -> the own cells' sums in phi_red, and the
+// local accumulator is cleared for the next sweep.
 int
 doma_b200_allreduce_phi_cur(doma_b200_ctx * c)
 {
   ENTER(c);
   if (!c->nccl_comm)
     return 0; // single rank
-  const int r = g_nccl.AllReduce(c->phi_cur, c->phi_cur, (size_t)c->N, /*ncclDouble*/ 8, /*ncclSum*/ 0, c->nccl_comm, c->stream);
+  int r = 0;
+  if (c->cell_sharded)
+  {
+    r = g_nccl.ReduceScatter(c->phi_cur, c->phi_red, (size_t)c->slice, /*ncclDouble*/ 8, /*ncclSum*/ 0, c->nccl_comm, c->stream);
+    if (!r)
+      DOMA_CUDA(c, cudaMemsetAsync(c->phi_cur, 0, sizeof(double) * c->N, c->stream));
+    c->phi_cur_reduced = true;
+  }
+  else
+    r = g_nccl.AllReduce(c->phi_cur, c->phi_cur, (size_t)c->N, /*ncclDouble*/ 8, /*ncclSum*/ 0, c->nccl_comm, c->stream);
   if (r)
   {
-    snprintf(c->err, DOMA_MAX_ERR, "ncclAllReduce: %s", g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "?");
+    snprintf(c->err, DOMA_MAX_ERR, "%s: %s", c->cell_sharded ? "ncclReduceScatter" : "ncclAllReduce", g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "?");
     return 24;
   }
   c->launches += 1;
@@ -1126,3 +1298,33 @@ doma_b200_allreduce_phi_cur(doma_b200_ctx * c)
 }
 
 } // extern "C"
+
+// ---- collectives the other translation units use ----
+int
+doma_comm_gather_q(doma_b200_ctx * c)
+{
+  if (!c->cell_sharded || !c->q_slice_only)
+    return 0;
+  const int r = g_nccl.AllGather(c->q + c->cell_lo, c->q, (size_t)c->slice, /*ncclDouble*/ 8, c->nccl_comm, c->stream);
+  if (r)
+  {
+    snprintf(c->err, DOMA_MAX_ERR, "ncclAllGather(q): %s", g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "?");
+    return 24;
+  }
+  c->launches += 1;
+  c->q_slice_only = false;
+  return 0;
+}
+
+int
+doma_comm_sum_pair(doma_b200_ctx * c)
+{
+  const int r = g_nccl.AllReduce(c->red_out, c->red_out, 2, /*ncclDouble*/ 8, /*ncclSum*/ 0, c->nccl_comm, c->stream);
+  if (r)
+  {
+    snprintf(c->err, DOMA_MAX_ERR, "ncclAllReduce(pair): %s", g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "?");
+    return 24;
+  }
+  c->launches += 1;
+  return 0;
+}

@@ -99,6 +99,16 @@ struct doma_b200_ctx
   // NCCL (resolved with dlopen at comm_init; see api.cu)
   void * nccl_comm;
   int rank, nranks;
+  // Cell sharding of the elementwise phases across the ranks of an angle-sharded run (api.cu, comm_init): the sweep
+  // needs q on every cell and adds into phi_cur on every cell, but everything else is per cell, so rank r keeps
+  // the state of cells [cell_lo, cell_hi) only:  all-gather(q) -> sweep -> reduce-scatter(phi_cur) -> residual /
+  // update / source build on the own cells.  Same NVLink bytes as one all-reduce, elementwise work / P.
+  bool cell_sharded;
+  int64_t cell_lo, cell_hi, slice; // slice = cells per rank, nranks * slice >= N (arrays are padded for it)
+  double * phi_red;                // [slice] the summed increment of the own cells (what the residual / update kernels read)
+  double * gather_tmp;             // [nranks * slice] scratch: get_array / dumps gather the slices here
+  bool q_slice_only;               // q is current on the own cells only: all-gather before the next sweep
+  bool phi_cur_reduced;            // phi_red holds the summed increment; the local accumulator phi_cur is zero again
 
   char err[DOMA_MAX_ERR];
 };
@@ -113,6 +123,16 @@ struct doma_b200_ctx
       return 100 + (int)e_;                                                                                      \
     }                                                                                                            \
   } while (0)
+
+#define DOMA_PAD 1024 // doubles of padding behind every per-cell array (nranks * slice - N <= 2 * nranks)
+// the cells the elementwise kernels of this rank work on, and the increment they read
+static inline int64_t ew_lo(const doma_b200_ctx * c) { return c->cell_sharded ? c->cell_lo : 0; }
+static inline int64_t ew_hi(const doma_b200_ctx * c) { return c->cell_sharded ? c->cell_hi : c->N; }
+static inline double * ew_phi_cur(const doma_b200_ctx * c) { return c->cell_sharded ? c->phi_red - c->cell_lo : c->phi_cur; }
+
+// api.cu: collectives of the cell-sharded mode (no-ops otherwise)
+int doma_comm_gather_q(doma_b200_ctx * c);              // all-gather(q) if only the own cells are current
+int doma_comm_sum_pair(doma_b200_ctx * c);              // red_out[0..1] summed over ranks (identical bits on every rank)
 
 // elementwise.cu
 int doma_launch_reset_state(doma_b200_ctx * c, double phi_init);

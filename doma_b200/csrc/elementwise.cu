@@ -57,10 +57,10 @@ fill_kernel(double * __restrict__ p, int64_t n, double v)
 // device-to-device moves of the asynchronous host-buffer sweeps, as kernels: a cudaMemcpyAsync D2D may be put on the
 // copy engine that is busy with the neighbouring group's PCIe transfer and then waits 2.5 ms for it (measured)
 __global__ void
-stage_in_kernel(double * __restrict__ q, const double * __restrict__ q_stage, double * __restrict__ phi_cur, int64_t n)
+stage_in_kernel(double * __restrict__ q, const double * __restrict__ q_stage, double * __restrict__ phi_cur, int64_t lo, int64_t hi)
 {
-  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n)
+  const int64_t i = lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < hi)
   {
     q[i] = q_stage[i];
     phi_cur[i] = 0.0;
@@ -77,12 +77,12 @@ copy_kernel(double * __restrict__ dst, const double * __restrict__ src, int64_t 
 
 // stepDNPs (3D:236-260)
 __global__ void
-step_dnps_kernel(int64_t N, int G, int D, double dt, const int32_t * __restrict__ mat, const int32_t * __restrict__ n_delayed,
+step_dnps_kernel(int64_t N, int64_t lo, int64_t hi, int G, int D, double dt, const int32_t * __restrict__ mat, const int32_t * __restrict__ n_delayed,
                  const double * __restrict__ nu_sigma_f, const double * __restrict__ beta, const double * __restrict__ lambda,
                  const double * __restrict__ phi_tot, double * __restrict__ dnp_cur, double * __restrict__ dnp_last)
 {
-  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= N)
+  const int64_t i = lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= hi)
     return;
   const int m = mat[i];
   const int nd = n_delayed[m];
@@ -103,7 +103,7 @@ step_dnps_kernel(int64_t N, int G, int D, double dt, const int32_t * __restrict_
 // loads of phi_tot are issued up front instead of one per iteration behind an IEEE division.
 template <int GT>
 __global__ void
-mg_source_kernel(int64_t N, int G, int D, int g, double t, double f, int transient, double dt,
+mg_source_kernel(int64_t N, int64_t lo, int64_t hi, int G, int D, int g, double t, double f, int transient, double dt,
                  const int32_t * __restrict__ mat, const int32_t * __restrict__ mat_flags,
                  const int32_t * __restrict__ n_delayed, const int32_t * __restrict__ step_type,
                  const double * __restrict__ step_t_insert, const double * __restrict__ step_t_remove,
@@ -113,8 +113,8 @@ mg_source_kernel(int64_t N, int G, int D, int g, double t, double f, int transie
                  const double * __restrict__ dnp_cur, const double * __restrict__ phi_last, double * __restrict__ phi_tot,
                  double * __restrict__ phi_prev, double * __restrict__ q_out, double * __restrict__ phi_cur)
 {
-  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= N)
+  const int64_t i = lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= hi)
     return;
   const int m = mat[i];
   const int nd = n_delayed[m];
@@ -175,14 +175,14 @@ mg_source_kernel(int64_t N, int G, int D, int g, double t, double f, int transie
 // updateMultigroupSourceEigen(g) (3D:404-430): "+=" onto the stale q
 template <int GT>
 __global__ void
-mg_source_eigen_kernel(int64_t N, int G, int g, double k, double f, const int32_t * __restrict__ mat,
+mg_source_eigen_kernel(int64_t N, int64_t lo, int64_t hi, int G, int g, double k, double f, const int32_t * __restrict__ mat,
                        const int32_t * __restrict__ mat_flags, const double * __restrict__ sigma_s,
                        const double * __restrict__ chi_p, const double * __restrict__ nu_sigma_f,
                        double * __restrict__ phi_tot, double * __restrict__ phi_prev, double * __restrict__ q_io,
                        double * __restrict__ phi_cur)
 {
-  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= N)
+  const int64_t i = lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= hi)
     return;
   const int m = mat[i];
   const bool has_chi = (mat_flags[m] & DOMA_MAT_HAS_CHI_P) != 0;
@@ -212,12 +212,12 @@ mg_source_eigen_kernel(int64_t N, int G, int g, double k, double f, const int32_
 
 // updateScatteringSource(g) (3D:531-545)
 __global__ void
-scatter_source_kernel(int64_t N, int G, int g, double f, const int32_t * __restrict__ mat,
+scatter_source_kernel(int64_t N, int64_t lo, int64_t hi, int G, int g, double f, const int32_t * __restrict__ mat,
                       const double * __restrict__ sigma_s, double * __restrict__ phi_tot_g, double * __restrict__ q,
                       double * __restrict__ phi_cur)
 {
-  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= N)
+  const int64_t i = lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= hi)
     return;
   const int m = mat[i];
   const double cur = phi_cur[i];
@@ -275,11 +275,11 @@ block_reduce2(double a, double b, double * __restrict__ partial, int slot)
 
 // computeScatteringResidual(g) (3D:547-563): sum V*cur^2, sum V*(tot+cur)^2
 __global__ void
-scatter_residual_kernel(int64_t N, Geo geo, const double * __restrict__ phi_tot_g, const double * __restrict__ phi_cur,
+scatter_residual_kernel(int64_t lo, int64_t hi, Geo geo, const double * __restrict__ phi_tot_g, const double * __restrict__ phi_cur,
                         double * __restrict__ partial)
 {
   double diff = 0.0, total = 0.0;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < N; i += (int64_t)gridDim.x * blockDim.x)
+  for (int64_t i = lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += (int64_t)gridDim.x * blockDim.x)
   {
     const double v = geo.measure(i);
     const double cur = phi_cur[i], s = phi_tot_g[i] + cur;
@@ -294,12 +294,12 @@ scatter_residual_kernel(int64_t N, Geo geo, const double * __restrict__ phi_tot_
 // order as the two separate kernels, so residual and state are bit-identical to the unfused path.
 // 16 B read + 24 B written per cell instead of 32 B + 24 B.
 __global__ void
-scatter_residual_update_kernel(int64_t N, int G, int g, double f, Geo geo, const int32_t * __restrict__ mat,
+scatter_residual_update_kernel(int64_t lo, int64_t hi, int G, int g, double f, Geo geo, const int32_t * __restrict__ mat,
                                const double * __restrict__ sigma_s, double * __restrict__ phi_tot_g,
                                double * __restrict__ phi_cur, double * __restrict__ q, double * __restrict__ partial)
 {
   double diff = 0.0, total = 0.0;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < N; i += (int64_t)gridDim.x * blockDim.x)
+  for (int64_t i = lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += (int64_t)gridDim.x * blockDim.x)
   {
     const double v = geo.measure(i);
     const double cur = phi_cur[i], s = phi_tot_g[i] + cur;
@@ -314,11 +314,11 @@ scatter_residual_update_kernel(int64_t N, int G, int g, double f, Geo geo, const
 
 // computeMGFluxResidual() (3D:318-337)
 __global__ void
-mg_residual_kernel(int64_t N, int G, Geo geo, const double * __restrict__ phi_tot, const double * __restrict__ phi_prev,
+mg_residual_kernel(int64_t N, int64_t lo, int64_t hi, int G, Geo geo, const double * __restrict__ phi_tot, const double * __restrict__ phi_prev,
                    double * __restrict__ partial)
 {
   double diff = 0.0, total = 0.0;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < N; i += (int64_t)gridDim.x * blockDim.x)
+  for (int64_t i = lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += (int64_t)gridDim.x * blockDim.x)
   {
     const double v = geo.measure(i);
     for (int g = 0; g < G; ++g)
@@ -333,12 +333,12 @@ mg_residual_kernel(int64_t N, int G, Geo geo, const double * __restrict__ phi_to
 
 // updateEigenvalue() (3D:432-456): num = sum V nuSf phi_tot, den = sum V nuSf phi_prev / k
 __global__ void
-k_sums_kernel(int64_t N, int G, double k, Geo geo, const int32_t * __restrict__ mat, const int32_t * __restrict__ mat_flags,
+k_sums_kernel(int64_t N, int64_t lo, int64_t hi, int G, double k, Geo geo, const int32_t * __restrict__ mat, const int32_t * __restrict__ mat_flags,
               const double * __restrict__ nu_sigma_f, const double * __restrict__ phi_tot,
               const double * __restrict__ phi_prev, double * __restrict__ partial)
 {
   double num = 0.0, den = 0.0;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < N; i += (int64_t)gridDim.x * blockDim.x)
+  for (int64_t i = lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += (int64_t)gridDim.x * blockDim.x)
   {
     const int m = mat[i];
     if (!(mat_flags[m] & DOMA_MAT_HAS_NU_SIGMA_F))
@@ -351,6 +351,14 @@ k_sums_kernel(int64_t N, int G, double k, Geo geo, const int32_t * __restrict__ 
     }
   }
   block_reduce2(num, den, partial, blockIdx.x);
+}
+
+__global__ void
+publish_pair_kernel(const double * __restrict__ out, double * __restrict__ out_host)
+{
+  out_host[0] = out[0];
+  out_host[1] = out[1];
+  __threadfence_system();
 }
 
 __global__ void
@@ -370,17 +378,31 @@ final_reduce_kernel(const double * __restrict__ partial, double * __restrict__ o
     // the pair also lands in pinned host memory straight from the kernel (zero-copy store): a 16-byte
     // cudaMemcpyAsync would queue on the D2H copy engine behind a 134 MB result transfer of an
     // asynchronous host-buffer sweep and cost the stream 2.5 ms (measured, scripts/e2e_probe.py)
-    out_host[w] = a;
-    __threadfence_system();
+    if (out_host)
+    {
+      out_host[w] = a;
+      __threadfence_system();
+    }
   }
 }
 
 int
 finish_reduce(doma_b200_ctx * c)
 {
-  final_reduce_kernel<<<1, 64, 0, c->stream>>>(c->red_partial, c->red_out, c->h_red_dev);
+  // cell-sharded ranks hold partial sums of their own cells: sum the pair over the ranks first (every rank gets the
+  // same bits, so every rank takes the same branch in the loops), then publish
+  final_reduce_kernel<<<1, 64, 0, c->stream>>>(c->red_partial, c->red_out, c->cell_sharded ? nullptr : c->h_red_dev);
   c->launches += 2;
   DOMA_CUDA(c, cudaGetLastError());
+  if (c->cell_sharded)
+  {
+    const int rc = doma_comm_sum_pair(c);
+    if (rc)
+      return rc;
+    publish_pair_kernel<<<1, 1, 0, c->stream>>>(c->red_out, c->h_red_dev);
+    c->launches += 1;
+    DOMA_CUDA(c, cudaGetLastError());
+  }
   DOMA_CUDA(c, cudaStreamSynchronize(c->stream));
   return 0;
 }
@@ -396,22 +418,38 @@ doma_launch_reset_state(doma_b200_ctx * c, double phi_init)
   DOMA_CUDA(c, cudaMemsetAsync(c->phi_prev, 0, sizeof(double) * GN, c->stream));
   DOMA_CUDA(c, cudaMemsetAsync(c->q, 0, sizeof(double) * c->N, c->stream));
   DOMA_CUDA(c, cudaMemsetAsync(c->phi_cur, 0, sizeof(double) * c->N, c->stream));
+  if (c->cell_sharded)
+  {
+    DOMA_CUDA(c, cudaMemsetAsync(c->phi_red, 0, sizeof(double) * c->slice, c->stream));
+    c->q_slice_only = false;
+    c->phi_cur_reduced = true;
+  }
   return 0;
 }
 
 int
 doma_launch_stage_in(doma_b200_ctx * c)
 {
-  stage_in_kernel<<<ew_blocks(c->N), EW_THREADS, 0, c->stream>>>(c->q, c->q_stage, c->phi_cur, c->N);
+  const int64_t lo = ew_lo(c), hi = ew_hi(c);
+  stage_in_kernel<<<ew_blocks(hi - lo), EW_THREADS, 0, c->stream>>>(c->q, c->q_stage, ew_phi_cur(c), lo, hi);
   c->launches += 1;
   DOMA_CUDA(c, cudaGetLastError());
+  if (c->cell_sharded)
+  {
+    if (!c->phi_cur_reduced) // a sweep without its reduction left partial sums in the local accumulator
+      DOMA_CUDA(c, cudaMemsetAsync(c->phi_cur, 0, sizeof(double) * c->N, c->stream));
+    c->q_slice_only = true;
+    c->phi_cur_reduced = true;
+  }
   return 0;
 }
 
 int
 doma_launch_snapshot_phi_cur(doma_b200_ctx * c)
 {
-  copy_kernel<<<ew_blocks(c->N), EW_THREADS, 0, c->stream>>>(c->phi_snap, c->phi_cur, c->N);
+  // cell-sharded: the summed increment of the own cells (the host buffer receives that slice)
+  const int64_t lo = ew_lo(c), hi = ew_hi(c);
+  copy_kernel<<<ew_blocks(hi - lo), EW_THREADS, 0, c->stream>>>(c->phi_snap + lo, ew_phi_cur(c) + lo, hi - lo);
   c->launches += 1;
   DOMA_CUDA(c, cudaGetLastError());
   return 0;
@@ -446,6 +484,12 @@ doma_launch_update_step_fluxes(doma_b200_ctx * c)
   DOMA_CUDA(c, cudaMemsetAsync(c->phi_tot, 0, sizeof(double) * GN, c->stream));
   DOMA_CUDA(c, cudaMemsetAsync(c->q, 0, sizeof(double) * c->N, c->stream));
   DOMA_CUDA(c, cudaMemsetAsync(c->phi_cur, 0, sizeof(double) * c->N, c->stream));
+  if (c->cell_sharded)
+  {
+    DOMA_CUDA(c, cudaMemsetAsync(c->phi_red, 0, sizeof(double) * c->slice, c->stream));
+    c->q_slice_only = false;
+    c->phi_cur_reduced = true;
+  }
   return 0;
 }
 
@@ -454,7 +498,7 @@ doma_launch_step_dnps(doma_b200_ctx * c)
 {
   if (c->D == 0 || !c->dnp_cur)
     return 0;
-  step_dnps_kernel<<<ew_blocks(c->N), EW_THREADS, 0, c->stream>>>(c->N, c->G, c->D, c->dt, c->mat, c->n_delayed, c->nu_sigma_f,
+  step_dnps_kernel<<<ew_blocks(ew_hi(c) - ew_lo(c)), EW_THREADS, 0, c->stream>>>(c->N, ew_lo(c), ew_hi(c), c->G, c->D, c->dt, c->mat, c->n_delayed, c->nu_sigma_f,
                                                                   c->beta, c->lambda, c->phi_tot, c->dnp_cur, c->dnp_last);
   c->launches += 1;
   DOMA_CUDA(c, cudaGetLastError());
@@ -467,10 +511,10 @@ doma_launch_update_mg_source(doma_b200_ctx * c, int g, double t)
   const double f = c->dims == 3 ? 0.25 : 0.5;
   const int transient = c->mode == DOMA_MODE_TRANSIENT;
 #define MGS(GT)                                                                                                          \
-  mg_source_kernel<GT><<<ew_blocks(c->N), EW_THREADS, 0, c->stream>>>(                                                   \
-      c->N, c->G, c->D, g, t, f, transient, c->dt, c->mat, c->mat_flags, c->n_delayed, c->step_type, c->step_t_insert, \
+  mg_source_kernel<GT><<<ew_blocks(ew_hi(c) - ew_lo(c)), EW_THREADS, 0, c->stream>>>(                                    \
+      c->N, ew_lo(c), ew_hi(c), c->G, c->D, g, t, f, transient, c->dt, c->mat, c->mat_flags, c->n_delayed, c->step_type, c->step_t_insert, \
       c->step_t_remove, c->step_src, c->src, c->sigma_s, c->chi_p, c->nu_sigma_f, c->beta, c->chi_d, c->lambda,        \
-      c->inv_v, c->dnp_cur, c->phi_last, c->phi_tot, c->phi_prev, c->q, c->phi_cur)
+      c->inv_v, c->dnp_cur, c->phi_last, c->phi_tot, c->phi_prev, c->q, ew_phi_cur(c))
   switch (c->G)
   {
     case 1: MGS(1); break;
@@ -486,6 +530,7 @@ doma_launch_update_mg_source(doma_b200_ctx * c, int g, double t)
 #undef MGS
   c->launches += 1;
   DOMA_CUDA(c, cudaGetLastError());
+  c->q_slice_only = c->cell_sharded;
   return 0;
 }
 
@@ -494,9 +539,9 @@ doma_launch_update_mg_source_eigen(doma_b200_ctx * c, int g, double k)
 {
   const double f = c->dims == 3 ? 0.25 : 0.5;
 #define MGE(GT)                                                                                                    \
-  mg_source_eigen_kernel<GT><<<ew_blocks(c->N), EW_THREADS, 0, c->stream>>>(c->N, c->G, g, k, f, c->mat, c->mat_flags, \
-                                                                            c->sigma_s, c->chi_p, c->nu_sigma_f,     \
-                                                                            c->phi_tot, c->phi_prev, c->q, c->phi_cur)
+  mg_source_eigen_kernel<GT><<<ew_blocks(ew_hi(c) - ew_lo(c)), EW_THREADS, 0, c->stream>>>(                        \
+      c->N, ew_lo(c), ew_hi(c), c->G, g, k, f, c->mat, c->mat_flags, c->sigma_s, c->chi_p, c->nu_sigma_f, c->phi_tot,  \
+      c->phi_prev, c->q, ew_phi_cur(c))
   switch (c->G)
   {
     case 1: MGE(1); break;
@@ -512,6 +557,7 @@ doma_launch_update_mg_source_eigen(doma_b200_ctx * c, int g, double k)
 #undef MGE
   c->launches += 1;
   DOMA_CUDA(c, cudaGetLastError());
+  c->q_slice_only = c->cell_sharded;
   return 0;
 }
 
@@ -519,18 +565,19 @@ int
 doma_launch_update_scatter_source(doma_b200_ctx * c, int g)
 {
   const double f = c->dims == 3 ? 0.25 : 0.5;
-  scatter_source_kernel<<<ew_blocks(c->N), EW_THREADS, 0, c->stream>>>(c->N, c->G, g, f, c->mat, c->sigma_s,
-                                                                       c->phi_tot + (int64_t)g * c->N, c->q, c->phi_cur);
+  scatter_source_kernel<<<ew_blocks(ew_hi(c) - ew_lo(c)), EW_THREADS, 0, c->stream>>>(
+      c->N, ew_lo(c), ew_hi(c), c->G, g, f, c->mat, c->sigma_s, c->phi_tot + (int64_t)g * c->N, c->q, ew_phi_cur(c));
   c->launches += 1;
   DOMA_CUDA(c, cudaGetLastError());
+  c->q_slice_only = c->cell_sharded;
   return 0;
 }
 
 int
 doma_launch_scatter_residual(doma_b200_ctx * c, int g)
 {
-  scatter_residual_kernel<<<RED_BLOCKS, EW_THREADS, 0, c->stream>>>(c->N, geo_of(c), c->phi_tot + (int64_t)g * c->N, c->phi_cur,
-                                                                    c->red_partial);
+  scatter_residual_kernel<<<RED_BLOCKS, EW_THREADS, 0, c->stream>>>(ew_lo(c), ew_hi(c), geo_of(c), c->phi_tot + (int64_t)g * c->N,
+                                                                    ew_phi_cur(c), c->red_partial);
   DOMA_CUDA(c, cudaGetLastError());
   return finish_reduce(c);
 }
@@ -539,17 +586,19 @@ int
 doma_launch_scatter_residual_update(doma_b200_ctx * c, int g)
 {
   const double f = c->dims == 3 ? 0.25 : 0.5;
-  scatter_residual_update_kernel<<<RED_BLOCKS, EW_THREADS, 0, c->stream>>>(c->N, c->G, g, f, geo_of(c), c->mat, c->sigma_s,
-                                                                           c->phi_tot + (int64_t)g * c->N, c->phi_cur, c->q,
-                                                                           c->red_partial);
+  scatter_residual_update_kernel<<<RED_BLOCKS, EW_THREADS, 0, c->stream>>>(ew_lo(c), ew_hi(c), c->G, g, f, geo_of(c), c->mat,
+                                                                           c->sigma_s, c->phi_tot + (int64_t)g * c->N,
+                                                                           ew_phi_cur(c), c->q, c->red_partial);
   DOMA_CUDA(c, cudaGetLastError());
+  c->q_slice_only = c->cell_sharded;
   return finish_reduce(c);
 }
 
 int
 doma_launch_mg_residual(doma_b200_ctx * c)
 {
-  mg_residual_kernel<<<RED_BLOCKS, EW_THREADS, 0, c->stream>>>(c->N, c->G, geo_of(c), c->phi_tot, c->phi_prev, c->red_partial);
+  mg_residual_kernel<<<RED_BLOCKS, EW_THREADS, 0, c->stream>>>(c->N, ew_lo(c), ew_hi(c), c->G, geo_of(c), c->phi_tot, c->phi_prev,
+                                                               c->red_partial);
   DOMA_CUDA(c, cudaGetLastError());
   return finish_reduce(c);
 }
@@ -557,8 +606,8 @@ doma_launch_mg_residual(doma_b200_ctx * c)
 int
 doma_launch_k_sums(doma_b200_ctx * c, double k)
 {
-  k_sums_kernel<<<RED_BLOCKS, EW_THREADS, 0, c->stream>>>(c->N, c->G, k, geo_of(c), c->mat, c->mat_flags, c->nu_sigma_f,
-                                                          c->phi_tot, c->phi_prev, c->red_partial);
+  k_sums_kernel<<<RED_BLOCKS, EW_THREADS, 0, c->stream>>>(c->N, ew_lo(c), ew_hi(c), c->G, k, geo_of(c), c->mat, c->mat_flags,
+                                                          c->nu_sigma_f, c->phi_tot, c->phi_prev, c->red_partial);
   DOMA_CUDA(c, cudaGetLastError());
   return finish_reduce(c);
 }

@@ -242,6 +242,7 @@ struct DriverConfig
   // BrickMesh::dumpToTextFile (same bytes, tests/test_text_output.py), and computeMGFluxResidual no longer copies
   // the flux into the per-cell host vectors after every outer iteration.
   bool fast_dump = false;
+  bool output_enabled = true; // false with --no-output (the same on every rank; only rank 0 has a file base)
   // flat mesh (--flat, automatic above 2 M cells in steady / eigenvalue runs): geometry and block ids come from
   // FlatProblem::setGeometryFromParams, the solver is handed a stub mesh of one cell per block; implies --fast-dump
   bool flat_mesh = false;

@@ -193,6 +193,7 @@ main(int argc, char ** argv)
   const auto params = parseInputParameters(inp_path.string());
   omp_set_num_threads(threads);
   config().scheme = params._eq_type == EquationType::DD ? DOMA_SCHEME_DD : DOMA_SCHEME_TWDD;
+  config().output_enabled = output;
   const std::string base = (output && root) ? (inp_path.parent_path() / inp_path.stem()).string() : std::string("");
   if (params._mode == RunMode::Transient && base.empty() && root)
     std::cerr << "note: transient runs always write per-step dumps (reference behaviour); they go to ./_t*" << std::endl;

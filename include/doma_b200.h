@@ -166,6 +166,17 @@ int doma_b200_source_iteration(doma_b200_ctx * ctx, int32_t g, double tol, int32
 int doma_b200_comm_unique_id(char * out128, int32_t len);
 int doma_b200_comm_init(doma_b200_ctx * ctx, int32_t rank, int32_t nranks, const char * unique_id128, int32_t len);
 int doma_b200_allreduce_phi_cur(doma_b200_ctx * ctx);
+/* Cell sharding (default ON after comm_init with nranks > 1): only the sweep needs every cell on every rank, so rank r
+ * keeps phi_tot / phi_prev / phi_last / the precursors of cells [lo, hi) = DOMA_INFO_CELL_LO / _HI only and runs the
+ * source build, residual, update and k kernels on those cells:
+ *     ncclAllGather(q) -> sweep -> ncclReduceScatter(phi_cur) -> fused residual + update on the own cells
+ * (the same NVLink bytes as one all-reduce, the elementwise work divided by nranks; the two partial sums of a reduction
+ * are summed with a 16-byte ncclAllReduce, so every rank sees identical bits and takes identical branches).
+ * Consequences for the caller, all ranks alike: doma_b200_get_array, doma_b200_dump_text[_async] and
+ * doma_b200_set_cell_sharding are COLLECTIVE (every rank calls them; dump_text with an empty file base takes part in the
+ * gather and writes nothing); the host-buffer sweeps move the own cells only (q_host[lo..hi) up, phi_cur_out[lo..hi) down).
+ * on = 0 restores the r01 scheme: in-place ncclAllReduce(phi_cur), every rank repeats the elementwise work. */
+int doma_b200_set_cell_sharding(doma_b200_ctx * ctx, int32_t on);
 
 /* reductions (each synchronises and returns scalars) ------------------------------------------- */
 /* computeScatteringResidual(g) (3D:547-563) */
@@ -204,7 +215,9 @@ enum
   DOMA_INFO_N_UNITS = 6,         /* sweep units = (octant, batch of <= 32 ordinates) */
   DOMA_INFO_N_TILES = 7,         /* tiles of the KBA decomposition */
   DOMA_INFO_TILE_Y = 8,          /* tile extents in cells (x extent is 8); chosen by the library unless set_tile was called */
-  DOMA_INFO_TILE_Z = 9
+  DOMA_INFO_TILE_Z = 9,
+  DOMA_INFO_CELL_LO = 10,        /* cells [lo, hi) whose state this rank keeps (0, N unless cell-sharded) */
+  DOMA_INFO_CELL_HI = 11
 };
 int doma_b200_get_info(doma_b200_ctx * ctx, int32_t what, int64_t * out);
 /* How the persistent sweep kernel hands tile-boundary face fluxes from the warp that produced them to the warp that
