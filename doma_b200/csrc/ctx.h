@@ -26,6 +26,15 @@ struct SweepUnit
   int n_lanes; // ordinates in this unit, <= 32
 };
 
+#define DOMA_SI_HIST 2048
+struct SiState
+{
+  int it;    // iterations completed
+  int stop;  // set by the closing kernel once !(it < max_it && tol < residual): the remaining enqueued kernels return at once
+  double res;
+  double hist[DOMA_SI_HIST];
+};
+
 struct doma_b200_ctx
 {
   int device;
@@ -42,8 +51,8 @@ struct doma_b200_ctx
   int32_t *mat_flags, *n_delayed, *step_type;
   double *sigma_t, *sigma_s, *nu_sigma_f, *chi_p, *src, *inv_v, *chi_d, *beta, *lambda;
   double *step_t_insert, *step_t_remove, *step_src;
-  double * sig_cell;  // [N] total cross section the cell solve uses, expanded per cell for the group being swept
-  int sig_cell_group; // group sig_cell currently holds, -1 = none
+  double * sig_cell;  // [G][N] total cross section the cell solve uses, expanded per cell (built once, elementwise.cu)
+  int sig_cell_group; // G once sig_cell has been built, -1 before
 
   // state
   double *phi_tot, *phi_prev, *phi_last, *dnp_cur, *dnp_last, *q, *phi_cur;
@@ -66,6 +75,7 @@ struct doma_b200_ctx
   int variant;                // DOMA_SWEEP_AUTO / _FLAGS / _LL as requested (doma_b200_set_sweep_variant)
   bool use_ll;                // doma_choose_tile's protocol choice when variant is AUTO
   bool last_sweep_ll;         // protocol of the most recent sweep
+  int max_blocks;             // > 0: cap on the CTAs of a sweep launch (experiments: DOMA_B200_MAX_BLOCKS at create)
   int ll_epoch;               // LL tag epoch (20 bits; the planes are cleared when it wraps)
   bool planes_raw;            // the face planes were last written by a FLAGS sweep (raw doubles, no tags)
   int ntx, nty, ntz, n_tiles;
@@ -81,6 +91,12 @@ struct doma_b200_ctx
   double * red_out;     // [2] device
   double * h_red;       // [2] pinned, mapped host memory
   double * h_red_dev;   // the device-side address of h_red (final_reduce_kernel stores into it)
+
+  // device-side source iteration (doma_b200_source_iteration on a single rank): iteration count, stop flag and the
+  // residual history live in pinned, mapped host memory that the closing kernel of every iteration writes
+  struct SiState * si;      // pinned host mirror (written by the closing kernel with zero-copy stores)
+  struct SiState * si_host_dev; // device address of the mirror
+  struct SiState * si_dev;  // the state the kernels read, in device memory
 
   // timing / accounting
   cudaEvent_t ev0, ev1;
@@ -146,6 +162,9 @@ int doma_launch_stage_in(doma_b200_ctx * c);          // q = q_stage, phi_cur = 
 int doma_launch_snapshot_phi_cur(doma_b200_ctx * c);  // phi_snap = phi_cur
 int doma_launch_scatter_residual(doma_b200_ctx * c, int g); // leaves (diff, total) in h_red after sync
 int doma_launch_scatter_residual_update(doma_b200_ctx * c, int g); // fused pair, leaves (diff, total) in h_red
+// one iteration of the device-side loop: fused residual + update (skipped when si->stop), then the closing kernel that
+// turns the sums into the residual, appends it to the history and decides whether the loop goes on; no synchronisation
+int doma_launch_si_iteration_tail(doma_b200_ctx * c, int g, double tol, int max_it);
 int doma_launch_mg_residual(doma_b200_ctx * c);
 int doma_launch_k_sums(doma_b200_ctx * c, double k);
 int doma_launch_sig_eff(doma_b200_ctx * c, int g);
@@ -157,5 +176,6 @@ int doma_build_units(doma_b200_ctx * c);
 int doma_sweep_setup_tiles(doma_b200_ctx * c, int ty, int tz);
 int doma_choose_tile(doma_b200_ctx * c);
 bool doma_sweep_uses_ll(const doma_b200_ctx * c);
-int doma_launch_sweep(doma_b200_ctx * c, int g);
+// stop: device flag, non-zero = the kernel returns at once; timed = false keeps the events of an earlier launch
+int doma_launch_sweep(doma_b200_ctx * c, int g, const int * stop = nullptr, bool timed = true);
 int doma_sweep_check(doma_b200_ctx * c); // check mode: every tile done, phi_cur finite (synchronises)

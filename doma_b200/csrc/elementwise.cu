@@ -29,14 +29,36 @@ struct Geo
 {
   const double *dx, *dy, *dz;
   int nx, ny, dims;
-  // CartesianCell3D::_volume = l_x*l_y*l_z (src/CartesianCell3D.cpp:19); 2D: _area = l_x*l_y
-  __device__ double measure(int64_t id) const
+};
+
+// Walks the cells id0, id0 + stride, id0 + 2 stride, ... of a grid-stride loop and yields each cell's measure
+// (CartesianCell3D::_volume = l_x*l_y*l_z, src/CartesianCell3D.cpp:19; 2D: _area = l_x*l_y) without a 64-bit
+// division per cell: (i, j, k) is divided out once, then advanced by the precomputed digits of the stride with carries.
+struct CellWalk
+{
+  const Geo & g;
+  int i, j, k, si, sj, sk;
+  __device__ CellWalk(const Geo & geo, int64_t id0, int64_t stride) : g(geo)
   {
-    const int i = (int)(id % nx);
-    const int64_t r = id / nx;
-    const int j = (int)(r % ny);
-    const int k = (int)(r / ny);
-    return dims == 3 ? dx[i] * dy[j] * dz[k] : dx[i] * dy[j];
+    i = (int)(id0 % geo.nx);
+    const int64_t r = id0 / geo.nx;
+    j = (int)(r % geo.ny);
+    k = (int)(r / geo.ny);
+    si = (int)(stride % geo.nx);
+    const int64_t rs = stride / geo.nx;
+    sj = (int)(rs % geo.ny);
+    sk = (int)(rs / geo.ny);
+  }
+  __device__ double measure() const { return g.dims == 3 ? g.dx[i] * g.dy[j] * g.dz[k] : g.dx[i] * g.dy[j]; }
+  __device__ void next()
+  {
+    i += si;
+    int c = i >= g.nx;
+    i -= c ? g.nx : 0;
+    j += sj + c;
+    c = j >= g.ny;
+    j -= c ? g.ny : 0;
+    k += sk + c;
   }
 };
 
@@ -228,7 +250,7 @@ scatter_source_kernel(int64_t N, int64_t lo, int64_t hi, int G, int g, double f,
 
 // total cross section seen by the cell solve for group g, expanded per cell so the sweep reads it
 // without the material indirection: sigma_t, plus inv_v/dt for 2D transients (the 3D sweeps never
-// pass mode/dt to the cell solve).  12 B per cell per sweep against the sweep's hundreds.
+// pass mode/dt to the cell solve).  Run once per group at the first sweep (doma_launch_sig_eff).
 __global__ void
 sig_cell_kernel(int64_t N, int G, int g, int add_inv_v, double dt, const int32_t * __restrict__ mat,
                 const double * __restrict__ sigma_t, const double * __restrict__ inv_v, double * __restrict__ sig_cell)
@@ -279,9 +301,11 @@ scatter_residual_kernel(int64_t lo, int64_t hi, Geo geo, const double * __restri
                         double * __restrict__ partial)
 {
   double diff = 0.0, total = 0.0;
-  for (int64_t i = lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += (int64_t)gridDim.x * blockDim.x)
+  const int64_t first = lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (int64_t)gridDim.x * blockDim.x;
+  CellWalk walk(geo, first < hi ? first : 0, stride);
+  for (int64_t i = first; i < hi; i += stride, walk.next())
   {
-    const double v = geo.measure(i);
+    const double v = walk.measure();
     const double cur = phi_cur[i], s = phi_tot_g[i] + cur;
     diff = diff + (cur * cur) * v;
     total = total + (s * s) * v;
@@ -296,12 +320,17 @@ scatter_residual_kernel(int64_t lo, int64_t hi, Geo geo, const double * __restri
 __global__ void
 scatter_residual_update_kernel(int64_t lo, int64_t hi, int G, int g, double f, Geo geo, const int32_t * __restrict__ mat,
                                const double * __restrict__ sigma_s, double * __restrict__ phi_tot_g,
-                               double * __restrict__ phi_cur, double * __restrict__ q, double * __restrict__ partial)
+                               double * __restrict__ phi_cur, double * __restrict__ q, double * __restrict__ partial,
+                               const int * __restrict__ stop)
 {
+  if (stop && *stop)
+    return; // device-side source iteration: already converged
   double diff = 0.0, total = 0.0;
-  for (int64_t i = lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += (int64_t)gridDim.x * blockDim.x)
+  const int64_t first = lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (int64_t)gridDim.x * blockDim.x;
+  CellWalk walk(geo, first < hi ? first : 0, stride);
+  for (int64_t i = first; i < hi; i += stride, walk.next())
   {
-    const double v = geo.measure(i);
+    const double v = walk.measure();
     const double cur = phi_cur[i], s = phi_tot_g[i] + cur;
     diff = diff + (cur * cur) * v;
     total = total + (s * s) * v;
@@ -318,9 +347,11 @@ mg_residual_kernel(int64_t N, int64_t lo, int64_t hi, int G, Geo geo, const doub
                    double * __restrict__ partial)
 {
   double diff = 0.0, total = 0.0;
-  for (int64_t i = lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += (int64_t)gridDim.x * blockDim.x)
+  const int64_t first = lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (int64_t)gridDim.x * blockDim.x;
+  CellWalk walk(geo, first < hi ? first : 0, stride);
+  for (int64_t i = first; i < hi; i += stride, walk.next())
   {
-    const double v = geo.measure(i);
+    const double v = walk.measure();
     for (int g = 0; g < G; ++g)
     {
       const double s = phi_tot[g * N + i], d = s - phi_prev[g * N + i];
@@ -338,12 +369,14 @@ k_sums_kernel(int64_t N, int64_t lo, int64_t hi, int G, double k, Geo geo, const
               const double * __restrict__ phi_prev, double * __restrict__ partial)
 {
   double num = 0.0, den = 0.0;
-  for (int64_t i = lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += (int64_t)gridDim.x * blockDim.x)
+  const int64_t first = lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (int64_t)gridDim.x * blockDim.x;
+  CellWalk walk(geo, first < hi ? first : 0, stride);
+  for (int64_t i = first; i < hi; i += stride, walk.next())
   {
     const int m = mat[i];
     if (!(mat_flags[m] & DOMA_MAT_HAS_NU_SIGMA_F))
       continue;
-    const double v = geo.measure(i);
+    const double v = walk.measure();
     for (int g = 0; g < G; ++g)
     {
       num = num + v * nu_sigma_f[m * G + g] * phi_tot[g * N + i];
@@ -383,6 +416,43 @@ final_reduce_kernel(const double * __restrict__ partial, double * __restrict__ o
       out_host[w] = a;
       __threadfence_system();
     }
+  }
+}
+
+// Closing kernel of one device-side source iteration (sourceIteration, 3D:464-481): the two sums -> the residual exactly
+// as the host path forms it (3D:562: total > 1e-8 ? sqrt(diff)/sqrt(total) : 0; IEEE sqrt and division, this file is
+// compiled without FMA contraction), appended to the history; the loop condition (3D:481) decides whether the kernels
+// already enqueued for the next iterations still have work.
+__global__ void
+si_close_kernel(const double * __restrict__ partial, SiState * __restrict__ st, SiState * __restrict__ host, double tol, int max_it)
+{
+  __shared__ double sums[2];
+  if (st->stop)
+    return;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  double a = 0.0;
+  for (int i = lane; i < RED_BLOCKS; i += 32)
+    a += partial[w * RED_BLOCKS + i];
+  for (int o = 16; o > 0; o >>= 1)
+    a += __shfl_down_sync(0xffffffffu, a, o);
+  if (lane == 0)
+    sums[w] = a;
+  __syncthreads();
+  if (threadIdx.x == 0)
+  {
+    const double res = sums[1] > 1e-8 ? sqrt(sums[0]) / sqrt(sums[1]) : 0.0;
+    const int it = st->it;
+    const int stop = !(it + 1 < max_it && tol < res);
+    st->res = res;
+    st->it = it + 1;
+    st->stop = stop;
+    // mirror for the host (pinned, mapped): what it reads after the batch's synchronisation
+    if (it < DOMA_SI_HIST)
+      host->hist[it] = res;
+    host->res = res;
+    host->it = it + 1;
+    host->stop = stop;
+    __threadfence_system();
   }
 }
 
@@ -588,10 +658,24 @@ doma_launch_scatter_residual_update(doma_b200_ctx * c, int g)
   const double f = c->dims == 3 ? 0.25 : 0.5;
   scatter_residual_update_kernel<<<RED_BLOCKS, EW_THREADS, 0, c->stream>>>(ew_lo(c), ew_hi(c), c->G, g, f, geo_of(c), c->mat,
                                                                            c->sigma_s, c->phi_tot + (int64_t)g * c->N,
-                                                                           ew_phi_cur(c), c->q, c->red_partial);
+                                                                           ew_phi_cur(c), c->q, c->red_partial, nullptr);
   DOMA_CUDA(c, cudaGetLastError());
   c->q_slice_only = c->cell_sharded;
   return finish_reduce(c);
+}
+
+int
+doma_launch_si_iteration_tail(doma_b200_ctx * c, int g, double tol, int max_it)
+{
+  const double f = c->dims == 3 ? 0.25 : 0.5;
+  scatter_residual_update_kernel<<<RED_BLOCKS, EW_THREADS, 0, c->stream>>>(0, c->N, c->G, g, f, geo_of(c), c->mat, c->sigma_s,
+                                                                           c->phi_tot + (int64_t)g * c->N, c->phi_cur, c->q,
+                                                                           c->red_partial, &c->si_dev->stop);
+  DOMA_CUDA(c, cudaGetLastError());
+  si_close_kernel<<<1, 64, 0, c->stream>>>(c->red_partial, c->si_dev, c->si_host_dev, tol, max_it);
+  DOMA_CUDA(c, cudaGetLastError());
+  c->launches += 2;
+  return 0;
 }
 
 int
@@ -612,16 +696,23 @@ doma_launch_k_sums(doma_b200_ctx * c, double k)
   return finish_reduce(c);
 }
 
+// The total cross section the cell solve uses, per cell and per group, is static (materials, and dt for 2D transients,
+// are fixed at create): expanded ONCE for all groups, so a sweep only picks its group's array.  G x N doubles of HBM
+// (1 GB at 256^3 x 8 groups) instead of a 12-byte-per-cell pass in front of every sweep of a new group.
 int
 doma_launch_sig_eff(doma_b200_ctx * c, int g)
 {
+  (void)g;
+  if (c->sig_cell_group == c->G)
+    return 0; // built
   const int add = (c->dims == 2 && c->mode == DOMA_MODE_TRANSIENT) ? 1 : 0;
-  if (c->sig_cell_group == g)
-    return 0; // already expanded for this group (repeated source iterations of one group)
-  sig_cell_kernel<<<ew_blocks(c->N), EW_THREADS, 0, c->stream>>>(c->N, c->G, g, add, c->dt, c->mat, c->sigma_t, c->inv_v,
-                                                                 c->sig_cell);
-  c->launches += 1;
-  DOMA_CUDA(c, cudaGetLastError());
-  c->sig_cell_group = g;
+  for (int gg = 0; gg < c->G; ++gg)
+  {
+    sig_cell_kernel<<<ew_blocks(c->N), EW_THREADS, 0, c->stream>>>(c->N, c->G, gg, add, c->dt, c->mat, c->sigma_t, c->inv_v,
+                                                                   c->sig_cell + (int64_t)gg * c->N);
+    c->launches += 1;
+    DOMA_CUDA(c, cudaGetLastError());
+  }
+  c->sig_cell_group = c->G;
   return 0;
 }

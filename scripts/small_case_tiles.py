@@ -1,25 +1,37 @@
 #!/usr/bin/env python
-"""Sweep time of the small shipped cases per tile choice (the wavefront is never saturated there: the
-tile that minimises hyperplanes x task latency wins, not the one with most tasks in flight)."""
-import os, sys, time
+"""Sweep time of the small shipped cases per tile choice and face protocol (the wavefront is never saturated there:
+the tile that minimises hyperplanes x task latency wins, not the one with most tasks in flight).
+
+    python scripts/small_case_tiles.py [tr2d|asm|k1 ...] [--quick]
+
+DOMA_B200_LIB picks an experimental build, DOMA_B200_MAX_BLOCKS caps the CTAs of a launch."""
+import os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 import numpy as np
 import doma_b200 as d
 from doma_b200 import abi
 cases = os.path.join(ROOT, "tests", "golden", "cases")
-for f, tiles in [("full_tr2d_1step.xml", [(0, 0), (1, 1), (2, 1), (4, 1)]), ("full_asm_fs_3outer.xml", [(0, 0), (2, 2), (4, 2), (4, 4), (2, 4), (2, 1), (4, 1), (1, 2)]),
-                 ("full_k1.xml", [(0, 0), (2, 2), (4, 2), (4, 4), (4, 8)])]:
-  params, prob = d.load_case(os.path.join(cases, f))
-  for vname, variant in (("auto", abi.SWEEP_AUTO), ("flags", abi.SWEEP_FLAGS), ("ll", abi.SWEEP_LL)):
-    for ty, tz in (tiles if vname != "auto" else [(0, 0)]):
+quick = "--quick" in sys.argv
+want = [a for a in sys.argv[1:] if not a.startswith("--")]
+ALL = {"tr2d": ("full_tr2d_1step.xml", [(1, 1), (2, 1), (4, 1)], [("ll", 4, 1), ("ll", 2, 1), ("flags", 2, 1)]),
+       "asm": ("full_asm_fs_3outer.xml", [(2, 2), (4, 2), (4, 4), (2, 4), (2, 1), (4, 1), (1, 2)], [("flags", 4, 1), ("flags", 2, 1), ("ll", 4, 1), ("ll", 1, 2), ("ll", 4, 2)]),
+       "k1": ("full_k1.xml", [(2, 2), (4, 2), (4, 4), (4, 8)], [("flags", 4, 2), ("ll", 4, 2), ("ll", 4, 1)])}
+V = {"auto": abi.SWEEP_AUTO, "flags": abi.SWEEP_FLAGS, "ll": abi.SWEEP_LL}
+for key, (f, tiles, quick_list) in ALL.items():
+    if want and key not in want:
+        continue
+    params, prob = d.load_case(os.path.join(cases, f))
+    runs = [("auto", 0, 0)] + (quick_list if quick else [(v, ty, tz) for v in ("flags", "ll") for ty, tz in tiles])
+    for vname, ty, tz in runs:
         ctx = abi.Context(prob)
-        ctx.set_sweep_variant(variant)
+        ctx.set_sweep_variant(V[vname])
         if ty: ctx.set_tile(8, ty, tz)
         ctx.reset_state(0.0)
         ctx.set_array(abi.ARR_Q, 0, np.ones(prob.n_cells))
         ts = []
-        for _ in range(6):
+        for _ in range(8):
             ctx.sweep(0); ctx.synchronize(); ts.append(ctx.last_sweep_ms())
-        print(f, vname, "->", "ll" if ctx.info(abi.INFO_SWEEP_VARIANT) == abi.SWEEP_LL else "flags", "tile 8x%dx%d%s" % (ctx.info(abi.INFO_TILE_Y), ctx.info(abi.INFO_TILE_Z), "" if ty else " (auto)"), "units", ctx.info(abi.INFO_N_UNITS),
-              "sweep us %.0f" % (min(ts[1:]) * 1e3), flush=True)
+        print(key, vname, "->", "ll" if ctx.info(abi.INFO_SWEEP_VARIANT) == abi.SWEEP_LL else "flags", "tile 8x%dx%d%s" % (ctx.info(abi.INFO_TILE_Y), ctx.info(abi.INFO_TILE_Z), "" if ty else " (auto)"), "units", ctx.info(abi.INFO_N_UNITS),
+              "sweep us %.0f" % (min(ts[1:]) * 1e3), "median %.0f" % (float(np.median(ts[1:])) * 1e3), flush=True)
+        ctx.close()
