@@ -28,7 +28,7 @@ MAT_HAS_SRC, MAT_HAS_CHI_P, MAT_HAS_NU_SIGMA_F = 1, 2, 4
 ARR_PHI_TOT, ARR_PHI_PREV, ARR_PHI_LAST, ARR_DNP_CUR, ARR_DNP_LAST, ARR_Q, ARR_PHI_CUR = range(7)
 SWEEP_AUTO, SWEEP_FLAGS, SWEEP_LL = 0, 1, 2
 (INFO_KERNEL_LAUNCHES, INFO_SWEEP_VARIANT, INFO_N_CELLS, INFO_N_ORD, INFO_FACE_BYTES, INFO_DEVICE_BYTES, INFO_N_UNITS, INFO_N_TILES,
- INFO_TILE_Y, INFO_TILE_Z, INFO_CELL_LO, INFO_CELL_HI) = range(12)
+ INFO_TILE_Y, INFO_TILE_Z, INFO_CELL_LO, INFO_CELL_HI, INFO_ROWS_PER_STEP) = range(13)
 
 _pd = C.POINTER(C.c_double)
 _pi = C.POINTER(C.c_int32)
@@ -199,6 +199,7 @@ class Library:
         "device_ptr": [C.c_void_p, C.c_int32, C.c_int32, C.POINTER(C.c_void_p)],
         "set_sweep_variant": [C.c_void_p, C.c_int32],
         "set_pairing": [C.c_void_p, C.c_int32],
+        "set_rows_per_step": [C.c_void_p, C.c_int32],
         "set_check": [C.c_void_p, C.c_int32],
         "last_sweep_ms": [C.c_void_p, C.POINTER(C.c_float)],
         "set_threads": [C.c_void_p, C.c_int32],
@@ -393,6 +394,7 @@ class Context:
         self._call("set_cell_sharding", int(bool(on)))
 
     def set_pairing(self, on: bool): self._call("set_pairing", int(bool(on)))
+    def set_rows_per_step(self, rows: int): self._call("set_rows_per_step", int(rows))
     def set_check(self, on: bool): self._call("set_check", int(bool(on)))
     def set_tile(self, tx: int, ty: int, tz: int): self._call("set_tile", int(tx), int(ty), int(tz))
 

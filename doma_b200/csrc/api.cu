@@ -206,6 +206,9 @@ create_impl(doma_b200_ctx * c, const doma_b200_problem * p)
   c->n_ord = p->n_ord;
   c->scheme = p->scheme, c->mode = p->mode, c->dt = p->dt;
   c->pairing_enabled = true;
+  c->rows2 = -1;
+  if (const char * r2 = getenv("DOMA_B200_ROWS2")) // experiments: 0 / 1 force the one-row / two-row kernel
+    c->rows2 = atoi(r2);
   if (const char * mb = getenv("DOMA_B200_MAX_BLOCKS")) // experiments only (scripts/small_case_grid.py)
     c->max_blocks = atoi(mb);
   c->variant = DOMA_SWEEP_AUTO;
@@ -925,6 +928,10 @@ doma_b200_get_info(doma_b200_ctx * c, int32_t what, int64_t * out)
     case DOMA_INFO_TILE_Z: *out = c->tile_z; break;
     case DOMA_INFO_CELL_LO: *out = ew_lo(c); break;
     case DOMA_INFO_CELL_HI: *out = ew_hi(c); break;
+    case DOMA_INFO_ROWS_PER_STEP:
+      doma_choose_rows(c);
+      *out = doma_sweep_uses_rows2(c) ? 2 : 1;
+      break;
     default: snprintf(c->err, DOMA_MAX_ERR, "get_info: unknown item %d", what); return 4;
   }
   return 0;
@@ -941,6 +948,19 @@ doma_b200_set_sweep_variant(doma_b200_ctx * c, int32_t variant)
   }
   c->variant = variant;
   return c->tile_auto ? doma_choose_tile(c) : 0; // the best tile depends on the protocol
+}
+
+int
+doma_b200_set_rows_per_step(doma_b200_ctx * c, int32_t rows)
+{
+  ENTER(c);
+  if (rows < 0 || rows > 2)
+  {
+    snprintf(c->err, DOMA_MAX_ERR, "set_rows_per_step: %d is none of 0 (automatic), 1, 2", rows);
+    return 4;
+  }
+  c->rows2 = rows == 0 ? -1 : rows - 1;
+  return 0;
 }
 
 int

@@ -75,6 +75,8 @@ struct doma_b200_ctx
   int variant;                // DOMA_SWEEP_AUTO / _FLAGS / _LL as requested (doma_b200_set_sweep_variant)
   bool use_ll;                // doma_choose_tile's protocol choice when variant is AUTO
   bool last_sweep_ll;         // protocol of the most recent sweep
+  int rows2;                  // two rows per step in the sweep (R2): -1 chooser, 0 off, 1 on (DOMA_B200_ROWS2 at create)
+  bool use_rows2;             // the chooser's answer
   int max_blocks;             // > 0: cap on the CTAs of a sweep launch (experiments: DOMA_B200_MAX_BLOCKS at create)
   int ll_epoch;               // LL tag epoch (20 bits; the planes are cleared when it wraps)
   bool planes_raw;            // the face planes were last written by a FLAGS sweep (raw doubles, no tags)
@@ -176,6 +178,8 @@ int doma_build_units(doma_b200_ctx * c);
 int doma_sweep_setup_tiles(doma_b200_ctx * c, int ty, int tz);
 int doma_choose_tile(doma_b200_ctx * c);
 bool doma_sweep_uses_ll(const doma_b200_ctx * c);
+bool doma_sweep_uses_rows2(const doma_b200_ctx * c);
+void doma_choose_rows(doma_b200_ctx * c);
 // stop: device flag, non-zero = the kernel returns at once; timed = false keeps the events of an earlier launch
 int doma_launch_sweep(doma_b200_ctx * c, int g, const int * stop = nullptr, bool timed = true);
 int doma_sweep_check(doma_b200_ctx * c); // check mode: every tile done, phi_cur finite (synchronises)

@@ -217,7 +217,8 @@ enum
   DOMA_INFO_TILE_Y = 8,          /* tile extents in cells (x extent is 8); chosen by the library unless set_tile was called */
   DOMA_INFO_TILE_Z = 9,
   DOMA_INFO_CELL_LO = 10,        /* cells [lo, hi) whose state this rank keeps (0, N unless cell-sharded) */
-  DOMA_INFO_CELL_HI = 11
+  DOMA_INFO_CELL_HI = 11,
+  DOMA_INFO_ROWS_PER_STEP = 12   /* rows of a slab the next sweep advances together: 1 or 2 (see set_rows_per_step) */
 };
 int doma_b200_get_info(doma_b200_ctx * ctx, int32_t what, int64_t * out);
 /* How the persistent sweep kernel hands tile-boundary face fluxes from the warp that produced them to the warp that
@@ -231,6 +232,11 @@ int doma_b200_get_info(doma_b200_ctx * ctx, int32_t what, int64_t * out);
  * Results are identical (same arithmetic, same order); only the timing differs. */
 enum { DOMA_SWEEP_AUTO = 0, DOMA_SWEEP_FLAGS = 1, DOMA_SWEEP_LL = 2 };
 int doma_b200_set_sweep_variant(doma_b200_ctx * ctx, int32_t variant);
+/* Rows of a tile slab a warp advances together (sweep.cu, template parameter R2): 1 = row after row, 16 warps per SM,
+ * best throughput when the wavefront fills the GPU; 2 = two rows skewed by one cell, two independent dependency chains
+ * per warp, 12 warps per SM, best when the sweep is a chain of task latencies; 0 (default) = the library picks from
+ * the tasks in flight per resident warp.  Results are identical bit for bit. */
+int doma_b200_set_rows_per_step(doma_b200_ctx * ctx, int32_t rows);
 /* Octant pairing: with <= 16 ordinates per octant two octants that differ only in the x direction share a warp,
  * 16 lanes each (default on; off = one octant per warp, for A/B tests).  Rebuilds the sweep units. */
 int doma_b200_set_pairing(doma_b200_ctx * ctx, int32_t on);

@@ -17,3 +17,8 @@ except Exception as e:
     print("$tag failed", e); print(open("gpurun_out/d_bench_n2_$tag.err").read()[-3000:])
 PY
 done
+# flat-builder start-up of the drop-in driver on the bench case (host-side; setup_seconds is the mesh construction)
+for f in --flat --no-flat; do
+  echo "== doma_b200_driver -i full_syn256_b.xml $f"
+  timeout 900 doma_b200/bin/doma_b200_driver -i tests/golden/cases/full_syn256_b.xml $f 2>&1 | grep -E "^DRIVER" | sed 's/ k=[^ ]*//'
+done 2>&1 | tee gpurun_out/d_driver_flat.txt

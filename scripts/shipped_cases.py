@@ -26,7 +26,7 @@ import doma_b200 as d  # noqa: E402
 from doma_b200 import abi  # noqa: E402
 
 
-def run(path, label, fused=True, ref_seconds=None, ref_threads=None):
+def run(path, label, fused=True, ref_seconds=None, ref_threads=None, ref_si=None):
     params, prob = d.load_case(path)
     ctx = abi.Context(prob)
     s = d.TransportSolver(ctx, params, fused_si=fused)
@@ -39,11 +39,15 @@ def run(path, label, fused=True, ref_seconds=None, ref_threads=None):
     row = {"case": label, "cells": prob.n_cells, "ordinates": prob.n_ord, "groups": params.num_groups, "sweeps": s.trace.sweeps,
            "ok": bool(ok), "k": s.k if params.mode == abi.MODE_EIGEN else None, "seconds": sec, "updates_per_s": upd / sec,
            "us_per_sweep": sec / max(s.trace.sweeps, 1) * 1e6, "units": ctx.info(abi.INFO_N_UNITS),
-           "tile": "8x%dx%d" % (ctx.info(abi.INFO_TILE_Y), ctx.info(abi.INFO_TILE_Z)), "inner_loop": "fused" if s.fused_si else "host"}
-    if ref_seconds:
+           "tile": "8x%dx%d" % (ctx.info(abi.INFO_TILE_Y), ctx.info(abi.INFO_TILE_Z)), "inner_loop": "fused" if s.fused_si else "host",
+           "protocol": "ll" if ctx.info(abi.INFO_SWEEP_VARIANT) == abi.SWEEP_LL else "flags", "rows_per_step": ctx.info(abi.INFO_ROWS_PER_STEP),
+           "si_counts_match_reference": None}
+    if ref_seconds and ref_seconds == ref_seconds:
         row["reference_seconds"] = ref_seconds
         row["reference_threads"] = ref_threads
         row["reference_where"] = "build container, 8 vCPU (tests/golden/full digest)"
+    if ref_si is not None:
+        row["si_counts_match_reference"] = list(s.trace.si_counts) == list(ref_si)   # identical iteration trace
     print(json.dumps(row), flush=True)
     return row
 
@@ -55,13 +59,16 @@ def main():
     a = ap.parse_args()
     rows = []
     cases = os.path.join(ROOT, "tests", "golden", "cases")
+    # untimed warm-up: module load, first-launch attribute calls and clocks must not land on the first (9-sweep) case
+    params, prob = d.load_case(os.path.join(cases, "full_k1.xml"))
+    d.TransportSolver(abi.Context(prob), params, fused_si=True).solve()
     for f in sorted(os.listdir(cases)):
         if not f.startswith("full_"):
             continue
         name = f[5:-4]
         g = np.load(os.path.join(ROOT, "tests", "golden", "full", name + ".npz"))
         for fused in (True, False):
-            rows.append(run(os.path.join(cases, f), "full_" + name, fused, float(g["ref_seconds"]), int(g["ref_threads"])))
+            rows.append(run(os.path.join(cases, f), "full_" + name, fused, float(g["ref_seconds"]), int(g["ref_threads"]), g["si_counts"].tolist()))
     if a.full:
         ref_cases = os.path.join(ROOT, "oracle", "_ref", "cases")
         for f in ("3D_assembly_fs.xml", "3D_assembly_eig.xml", "2D_assembly_fs.xml", "2D_assembly_eig.xml"):

@@ -70,15 +70,17 @@ SHAPES = [  # (shape, dims, scheme, npol, nazi, tile) incl. ragged tiles and lan
 ]
 
 
-PROTOCOLS = [(abi.SWEEP_FLAGS, False), (abi.SWEEP_LL, False), (abi.SWEEP_FLAGS, True), (abi.SWEEP_LL, True)]
-PROTOCOL_IDS = ["flags", "ll", "flags_check", "ll_check"]
+# (face protocol, check mode, rows per step): every instantiation family of sweep_kernel
+PROTOCOLS = [(abi.SWEEP_FLAGS, False, 1), (abi.SWEEP_LL, False, 1), (abi.SWEEP_FLAGS, True, 1), (abi.SWEEP_LL, True, 1),
+             (abi.SWEEP_FLAGS, False, 2), (abi.SWEEP_LL, False, 2), (abi.SWEEP_FLAGS, True, 2), (abi.SWEEP_LL, True, 2)]
+PROTOCOL_IDS = ["flags", "ll", "flags_check", "ll_check", "flags_r2", "ll_r2", "flags_r2_check", "ll_r2_check"]
 
 
-@pytest.mark.parametrize("variant,check", PROTOCOLS, ids=PROTOCOL_IDS)
+@pytest.mark.parametrize("variant,check,rows", PROTOCOLS, ids=PROTOCOL_IDS)
 @pytest.mark.parametrize("shape,dims,scheme,npol,nazi,tile", SHAPES)
-def test_single_sweep_matches_oracle(shape, dims, scheme, npol, nazi, tile, variant, check, cuda_lib, oracle_lib):
-    """Ragged shapes x both face hand-over protocols; `check` = poisoned face planes + completion / finiteness check
-    after every sweep (doma_b200_set_check), the dependency-miss detector."""
+def test_single_sweep_matches_oracle(shape, dims, scheme, npol, nazi, tile, variant, check, rows, cuda_lib, oracle_lib):
+    """Ragged shapes x both face hand-over protocols x one / two rows per step; `check` = poisoned face planes +
+    completion / finiteness check after every sweep (doma_b200_set_check), the dependency-miss detector."""
     mode = abi.MODE_TRANSIENT if dims == 2 else abi.MODE_FIXED
     prob = random_problem(shape, G=2, dims=dims, scheme=scheme, npol=npol, nazi=nazi, seed=sum(shape), mode=mode, dt=0.01)
     rng = np.random.default_rng(1)
@@ -90,6 +92,7 @@ def test_single_sweep_matches_oracle(shape, dims, scheme, npol, nazi, tile, vari
         if lib is cuda_lib:
             ctx.set_tile(8, *tile)
             ctx.set_sweep_variant(variant)
+            ctx.set_rows_per_step(rows)
             ctx.set_check(check)
         ctx.reset_state(0.0)
         ctx.set_array(abi.ARR_Q, 0, q)
@@ -99,6 +102,7 @@ def test_single_sweep_matches_oracle(shape, dims, scheme, npol, nazi, tile, vari
     assert np.all(np.isfinite(out[0])) and np.abs(out[0]).max() > 0
     assert relmax(out[1], out[0]) <= FLUX_RTOL
     assert ctx.info(abi.INFO_SWEEP_VARIANT) == variant
+    assert ctx.info(abi.INFO_ROWS_PER_STEP) == (rows if tile[0] >= 2 else 1)   # a one-row tile has no pair to advance
 
 
 @pytest.mark.parametrize("seed", range(24))
@@ -143,8 +147,9 @@ def test_random_problems_full_step_matches_oracle(seed, cuda_lib, oracle_lib):
 
 
 @pytest.mark.parametrize("dims,scheme,shape", [(3, 1, (21, 10, 9)), (3, 0, (8, 8, 8)), (2, 1, (30, 17, 1)), (3, 1, (5, 3, 2))])
+@pytest.mark.parametrize("rows", [1, 2], ids=["r1", "r2"])
 @pytest.mark.parametrize("variant", [abi.SWEEP_FLAGS, abi.SWEEP_LL], ids=["flags", "ll"])
-def test_octant_pairing_equals_unpaired(dims, scheme, shape, variant, cuda_lib, oracle_lib):
+def test_octant_pairing_equals_unpaired(dims, scheme, shape, variant, rows, cuda_lib, oracle_lib):
     """<= 16 ordinates per octant: two x-mirrored octants share a warp (sweep.cu PAIR).  Same flux as the unpaired
     units (doma_b200_set_pairing(0)) and as the oracle, half the units."""
     prob = random_problem(shape, G=1, dims=dims, scheme=scheme, npol=2, nazi=3, seed=shape[0])     # 12 per octant in 3D
@@ -153,6 +158,7 @@ def test_octant_pairing_equals_unpaired(dims, scheme, shape, variant, cuda_lib, 
         ctx = abi.Context(prob, lib)
         if lib is cuda_lib:
             ctx.set_sweep_variant(variant)
+            ctx.set_rows_per_step(rows)
             ctx.set_pairing(pairing)
         ctx.reset_state(0.0)
         ctx.set_array(abi.ARR_Q, 0, q)
