@@ -932,6 +932,7 @@ doma_b200_get_info(doma_b200_ctx * c, int32_t what, int64_t * out)
       doma_choose_rows(c);
       *out = doma_sweep_uses_rows2(c) ? 2 : 1;
       break;
+    case DOMA_INFO_SWEEP_BLOCKS: *out = c->last_blocks; break;
     default: snprintf(c->err, DOMA_MAX_ERR, "get_info: unknown item %d", what); return 4;
   }
   return 0;

@@ -78,6 +78,7 @@ struct doma_b200_ctx
   int rows2;                  // two rows per step in the sweep (R2): -1 chooser, 0 off, 1 on (DOMA_B200_ROWS2 at create)
   bool use_rows2;             // the chooser's answer
   int max_blocks;             // > 0: cap on the CTAs of a sweep launch (experiments: DOMA_B200_MAX_BLOCKS at create)
+  int last_blocks;            // CTAs of the last sweep launch (DOMA_INFO_SWEEP_BLOCKS)
   int ll_epoch;               // LL tag epoch (20 bits; the planes are cleared when it wraps)
   bool planes_raw;            // the face planes were last written by a FLAGS sweep (raw doubles, no tags)
   int ntx, nty, ntz, n_tiles;

@@ -218,7 +218,8 @@ enum
   DOMA_INFO_TILE_Z = 9,
   DOMA_INFO_CELL_LO = 10,        /* cells [lo, hi) whose state this rank keeps (0, N unless cell-sharded) */
   DOMA_INFO_CELL_HI = 11,
-  DOMA_INFO_ROWS_PER_STEP = 12   /* rows of a slab the next sweep advances together: 1 or 2 (see set_rows_per_step) */
+  DOMA_INFO_ROWS_PER_STEP = 12,  /* rows of a slab the next sweep advances together: 1 or 2 (see set_rows_per_step) */
+  DOMA_INFO_SWEEP_BLOCKS = 13    /* persistent CTAs (4 warps each) of the last sweep launch */
 };
 int doma_b200_get_info(doma_b200_ctx * ctx, int32_t what, int64_t * out);
 /* How the persistent sweep kernel hands tile-boundary face fluxes from the warp that produced them to the warp that
