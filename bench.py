@@ -418,7 +418,7 @@ def main():
            "ms_per_step": dt / a.steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
            "data": "synthetic", "config": config, "grind_ns": 1e9 / value, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
            "gpu_launches": int(launches), "clocks": clocks, "parity": parity, "wall_ms_per_step": wall / a.steps * 1e3,
-           "tile": "8x%dx%d%s" % (ctx.info(abi.INFO_TILE_Y), ctx.info(abi.INFO_TILE_Z), "" if a.tile else " (auto)"), "sweep_variant": {abi.SWEEP_FLAGS: "flags", abi.SWEEP_LL: "ll"}[int(ctx.info(abi.INFO_SWEEP_VARIANT))] + ("" if a.variant != "auto" else " (auto)"),
+           "tile": "%dx%dx%d%s" % (ctx.info(abi.INFO_TILE_X), ctx.info(abi.INFO_TILE_Y), ctx.info(abi.INFO_TILE_Z), "" if a.tile else " (auto)"), "sweep_variant": {abi.SWEEP_FLAGS: "flags", abi.SWEEP_LL: "ll"}[int(ctx.info(abi.INFO_SWEEP_VARIANT))] + ("" if a.variant != "auto" else " (auto)"),
            "units_per_rank": int(ctx.info(abi.INFO_N_UNITS)),
            "inner_loop": "doma_b200_source_iteration (library-owned)" if fused else "separate ABI calls",
            "exchange": ("none (1 GPU)" if world == 1 else

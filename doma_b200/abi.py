@@ -28,7 +28,7 @@ MAT_HAS_SRC, MAT_HAS_CHI_P, MAT_HAS_NU_SIGMA_F = 1, 2, 4
 ARR_PHI_TOT, ARR_PHI_PREV, ARR_PHI_LAST, ARR_DNP_CUR, ARR_DNP_LAST, ARR_Q, ARR_PHI_CUR = range(7)
 SWEEP_AUTO, SWEEP_FLAGS, SWEEP_LL = 0, 1, 2
 (INFO_KERNEL_LAUNCHES, INFO_SWEEP_VARIANT, INFO_N_CELLS, INFO_N_ORD, INFO_FACE_BYTES, INFO_DEVICE_BYTES, INFO_N_UNITS, INFO_N_TILES,
- INFO_TILE_Y, INFO_TILE_Z, INFO_CELL_LO, INFO_CELL_HI, INFO_ROWS_PER_STEP, INFO_SWEEP_BLOCKS) = range(14)
+ INFO_TILE_Y, INFO_TILE_Z, INFO_CELL_LO, INFO_CELL_HI, INFO_ROWS_PER_STEP, INFO_SWEEP_BLOCKS, INFO_TILE_X) = range(15)
 
 _pd = C.POINTER(C.c_double)
 _pi = C.POINTER(C.c_int32)

@@ -178,7 +178,7 @@ doma_build_units(doma_b200_ctx * c)
   memcpy(c->h_units, units.data(), sizeof(SweepUnit) * U);
   c->ll_epoch = 0; // the planes are zero again: LL tags restart
   if (!c->tile_auto && c->tile_y > 0 && c->tile_z > 0)
-    return doma_sweep_setup_tiles(c, c->tile_y, c->dims == 3 ? c->tile_z : 1); // keep a tile the caller chose
+    return doma_sweep_setup_tiles(c, c->tile_x, c->tile_y, c->dims == 3 ? c->tile_z : 1); // keep a tile the caller chose
   return doma_choose_tile(c);
 }
 
@@ -933,6 +933,7 @@ doma_b200_get_info(doma_b200_ctx * c, int32_t what, int64_t * out)
       *out = doma_sweep_uses_rows2(c) ? 2 : 1;
       break;
     case DOMA_INFO_SWEEP_BLOCKS: *out = c->last_blocks; break;
+    case DOMA_INFO_TILE_X: *out = c->tile_x; break;
     default: snprintf(c->err, DOMA_MAX_ERR, "get_info: unknown item %d", what); return 4;
   }
   return 0;
@@ -986,14 +987,14 @@ int
 doma_b200_set_tile(doma_b200_ctx * c, int32_t tx, int32_t ty, int32_t tz)
 {
   ENTER(c);
-  if (tx != 8)
-  {
-    snprintf(c->err, DOMA_MAX_ERR, "set_tile: the x extent of a tile is fixed to 8 (row held in registers)");
-    return 6;
-  }
   if (ty == 0 && tz == 0)
     return doma_choose_tile(c); // back to the library's own choice
-  return doma_sweep_setup_tiles(c, ty, tz);
+  if (tx != 8 && tx != 4)
+  {
+    snprintf(c->err, DOMA_MAX_ERR, "set_tile: the x extent of a tile is 8 or 4 (the row a warp holds in registers), not %d", tx);
+    return 6;
+  }
+  return doma_sweep_setup_tiles(c, tx, ty, tz);
 }
 
 int

@@ -70,7 +70,7 @@ struct doma_b200_ctx
   double *u_mu, *u_eta, *u_xi, *u_w; // [U][32] absolute direction cosines; padding lanes: 1,1,1,w=0
 
   // sweep scratch
-  int tile_x, tile_y, tile_z; // tile_x is fixed to 8 by the kernel (row held in registers)
+  int tile_x, tile_y, tile_z; // tile_x: 8 or 4, the row a warp holds in registers (template parameter of the kernel)
   bool tile_auto;             // tile (and protocol) chosen by doma_choose_tile (sweep.cu), not by set_tile
   int variant;                // DOMA_SWEEP_AUTO / _FLAGS / _LL as requested (doma_b200_set_sweep_variant)
   bool use_ll;                // doma_choose_tile's protocol choice when variant is AUTO
@@ -176,7 +176,7 @@ int doma_launch_sig_eff(doma_b200_ctx * c, int g);
 int doma_build_units(doma_b200_ctx * c);
 
 // sweep.cu
-int doma_sweep_setup_tiles(doma_b200_ctx * c, int ty, int tz);
+int doma_sweep_setup_tiles(doma_b200_ctx * c, int tx, int ty, int tz);
 int doma_choose_tile(doma_b200_ctx * c);
 bool doma_sweep_uses_ll(const doma_b200_ctx * c);
 bool doma_sweep_uses_rows2(const doma_b200_ctx * c);

@@ -214,12 +214,13 @@ enum
   DOMA_INFO_DEVICE_BYTES = 5,
   DOMA_INFO_N_UNITS = 6,         /* sweep units = (octant, batch of <= 32 ordinates) */
   DOMA_INFO_N_TILES = 7,         /* tiles of the KBA decomposition */
-  DOMA_INFO_TILE_Y = 8,          /* tile extents in cells (x extent is 8); chosen by the library unless set_tile was called */
+  DOMA_INFO_TILE_Y = 8,          /* tile extents in cells (x extent: DOMA_INFO_TILE_X); chosen by the library unless set_tile was called */
   DOMA_INFO_TILE_Z = 9,
   DOMA_INFO_CELL_LO = 10,        /* cells [lo, hi) whose state this rank keeps (0, N unless cell-sharded) */
   DOMA_INFO_CELL_HI = 11,
   DOMA_INFO_ROWS_PER_STEP = 12,  /* rows of a slab the next sweep advances together: 1 or 2 (see set_rows_per_step) */
-  DOMA_INFO_SWEEP_BLOCKS = 13    /* persistent CTAs (4 warps each) of the last sweep launch */
+  DOMA_INFO_SWEEP_BLOCKS = 13,   /* persistent CTAs (4 warps each) of the last sweep launch */
+  DOMA_INFO_TILE_X = 14          /* x extent of a tile: 8 or 4 cells */
 };
 int doma_b200_get_info(doma_b200_ctx * ctx, int32_t what, int64_t * out);
 /* How the persistent sweep kernel hands tile-boundary face fluxes from the warp that produced them to the warp that
@@ -246,7 +247,8 @@ int doma_b200_set_pairing(doma_b200_ctx * ctx, int32_t on);
  * that phi_cur is finite; a missed wavefront dependency then fails the call (error 30) instead of reading last
  * sweep's value.  Costs a synchronisation per sweep. */
 int doma_b200_set_check(doma_b200_ctx * ctx, int32_t on);
-/* KBA tile extents in cells; tx must be 8 (the row a warp keeps in registers), ty <= 4. Rebuilds the tile table.
+/* KBA tile extents in cells; tx is 8 or 4 (the row a warp keeps in registers), tx * ty <= 32; (tx, 0, 0) returns to the
+ * library's own choice. Rebuilds the tile table.
  * Without this call the library picks the tile from the mesh size and the number of sweep units (api.cu). */
 int doma_b200_set_tile(doma_b200_ctx * ctx, int32_t tx, int32_t ty, int32_t tz);
 /* device time in ms of the most recent doma_b200_sweep (CUDA events on the context's stream; synchronises) */

@@ -13,4 +13,4 @@ ctx.reset_state(0.0)
 ts = []
 for g in range(5):
     ctx.update_mg_source(g % 8, 0.0); ctx.sweep(g % 8); ctx.synchronize(); ts.append(ctx.last_sweep_ms()); ctx.update_scatter_source(g % 8)
-print(os.path.basename(os.environ.get("DOMA_B200_LIB", "default")), "%.3f" % min(ts[1:]), "tile 8x%dx%d" % (ctx.info(abi.INFO_TILE_Y), ctx.info(abi.INFO_TILE_Z)), flush=True)
+print(os.path.basename(os.environ.get("DOMA_B200_LIB", "default")), "%.3f" % min(ts[1:]), "tile %dx%dx%d" % (ctx.info(abi.INFO_TILE_X), ctx.info(abi.INFO_TILE_Y), ctx.info(abi.INFO_TILE_Z)), flush=True)

@@ -39,7 +39,7 @@ def run(path, label, fused=True, ref_seconds=None, ref_threads=None, ref_si=None
     row = {"case": label, "cells": prob.n_cells, "ordinates": prob.n_ord, "groups": params.num_groups, "sweeps": s.trace.sweeps,
            "ok": bool(ok), "k": s.k if params.mode == abi.MODE_EIGEN else None, "seconds": sec, "updates_per_s": upd / sec,
            "us_per_sweep": sec / max(s.trace.sweeps, 1) * 1e6, "units": ctx.info(abi.INFO_N_UNITS),
-           "tile": "8x%dx%d" % (ctx.info(abi.INFO_TILE_Y), ctx.info(abi.INFO_TILE_Z)), "inner_loop": "fused" if s.fused_si else "host",
+           "tile": "%dx%dx%d" % (ctx.info(abi.INFO_TILE_X), ctx.info(abi.INFO_TILE_Y), ctx.info(abi.INFO_TILE_Z)), "inner_loop": "fused" if s.fused_si else "host",
            "protocol": "ll" if ctx.info(abi.INFO_SWEEP_VARIANT) == abi.SWEEP_LL else "flags", "rows_per_step": ctx.info(abi.INFO_ROWS_PER_STEP),
            "si_counts_match_reference": None}
     if ref_seconds and ref_seconds == ref_seconds:

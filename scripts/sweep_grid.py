@@ -72,6 +72,6 @@ for W in [int(w) for w in a.worlds.split(",")]:
             t = sorted(ts[2:])
             upd = float(prob.n_cells) * prob.n_ord
             say(f"n {a.n} W {W} units {ctx.info(abi.INFO_N_UNITS)} ctas {ctx.info(abi.INFO_SWEEP_BLOCKS)} {vname:5s} -> {'ll' if ctx.info(abi.INFO_SWEEP_VARIANT) == abi.SWEEP_LL else 'flags'} "
-                f"tile 8x{ctx.info(abi.INFO_TILE_Y)}x{ctx.info(abi.INFO_TILE_Z)} sweep_ms min {t[0]:.3f} med {t[len(t) // 2]:.3f} "
+                f"tile {ctx.info(abi.INFO_TILE_X)}x{ctx.info(abi.INFO_TILE_Y)}x{ctx.info(abi.INFO_TILE_Z)} sweep_ms min {t[0]:.3f} med {t[len(t) // 2]:.3f} "
                 f"updates/s {upd / (t[0] * 1e-3):.4g} maxrel_vs_first {diff:.2e}")
     ctx.close()

@@ -52,6 +52,9 @@ def transient(name, xml_path):
 def snapshots(name, shipped, shape, groups, n_ord, threads, keep):
     """One digest per kept outer count n: the state after n outers of the unbounded run."""
     out_dir = os.path.join(T3, name)
+    if not os.path.isdir(out_dir):
+        print(name, "no run directory")
+        return
     log = open(os.path.join(T3, name + ".log")).read()
     done = sorted(int(d[5:]) for d in os.listdir(out_dir) if d.startswith("snap_") and os.path.exists(os.path.join(out_dir, d, "meta.json")))
     if not done:

@@ -67,6 +67,13 @@ SHAPES = [  # (shape, dims, scheme, npol, nazi, tile) incl. ragged tiles and lan
     ((19, 23, 1), 2, 1, 3, 3, (4, 1)),
     ((40, 37, 1), 2, 0, 2, 5, (2, 1)),
     ((1, 5, 1), 2, 1, 1, 1, (4, 1)),
+    # rows of 4 cells (tile = (tx, ty, tz)): ragged x extents, 8-row slabs, paired octants (<= 16 ordinates per octant), 2D
+    ((13, 7, 5), 3, 1, 2, 2, (4, 4, 8)),
+    ((21, 10, 7), 3, 1, 6, 7, (4, 8, 3)),
+    ((33, 17, 9), 3, 0, 5, 5, (4, 3, 2)),
+    ((16, 8, 16), 3, 1, 8, 8, (4, 4, 2)),
+    ((19, 23, 1), 2, 1, 3, 3, (4, 8, 1)),
+    ((40, 37, 1), 2, 0, 2, 5, (4, 1, 1)),
 ]
 
 
@@ -90,7 +97,7 @@ def test_single_sweep_matches_oracle(shape, dims, scheme, npol, nazi, tile, vari
     for lib in (oracle_lib, cuda_lib):
         ctx = abi.Context(prob, lib)
         if lib is cuda_lib:
-            ctx.set_tile(8, *tile)
+            ctx.set_tile(*(tile if len(tile) == 3 else (8,) + tile))
             ctx.set_sweep_variant(variant)
             ctx.set_rows_per_step(rows)
             ctx.set_check(check)
@@ -102,7 +109,8 @@ def test_single_sweep_matches_oracle(shape, dims, scheme, npol, nazi, tile, vari
     assert np.all(np.isfinite(out[0])) and np.abs(out[0]).max() > 0
     assert relmax(out[1], out[0]) <= FLUX_RTOL
     assert ctx.info(abi.INFO_SWEEP_VARIANT) == variant
-    assert ctx.info(abi.INFO_ROWS_PER_STEP) == (rows if tile[0] >= 2 else 1)   # a one-row tile has no pair to advance
+    assert ctx.info(abi.INFO_ROWS_PER_STEP) == (rows if tile[-2] >= 2 else 1)   # a one-row tile has no pair to advance
+    assert ctx.info(abi.INFO_TILE_X) == (tile[0] if len(tile) == 3 else 8)
 
 
 @pytest.mark.parametrize("seed", range(24))
@@ -125,7 +133,7 @@ def test_random_problems_full_step_matches_oracle(seed, cuda_lib, oracle_lib):
         if lib is cuda_lib:
             ctx.set_sweep_variant(variant)
             if tile:
-                ctx.set_tile(8, tile[0], tile[1] if dims == 3 else 1)
+                ctx.set_tile(4 if seed % 4 == 3 else 8, tile[0], tile[1] if dims == 3 else 1)
         ctx.reset_state(0.0)
         for g in range(G):
             ctx.set_array(abi.ARR_PHI_TOT, g, phi0[g])
