@@ -211,6 +211,10 @@ create_impl(doma_b200_ctx * c, const doma_b200_problem * p)
     c->rows2 = atoi(r2);
   if (const char * mb = getenv("DOMA_B200_MAX_BLOCKS")) // experiments only (scripts/small_case_grid.py)
     c->max_blocks = atoi(mb);
+  if (const char * ct = getenv("DOMA_B200_COMM_TIMING")) // measurement mode: per-collective device times, printed at destroy
+    c->comm_timing = *ct && *ct != '0';
+  if (c->comm_timing)
+    cudaMalloc(&c->comm_scratch, 16);
   c->variant = DOMA_SWEEP_AUTO;
   {
     const char * chk = getenv("DOMA_B200_CHECK"); // documented in include/doma_b200.h (doma_b200_set_check)
@@ -429,6 +433,10 @@ doma_b200_create(const doma_b200_problem * p, doma_b200_ctx ** out)
 int
 doma_b200_destroy(doma_b200_ctx * c)
 {
+  if (c && c->comm_timing && c->comm_calls[1])
+    fprintf(stderr, "doma_b200 comm timing (rank %d of %d, ms per call x calls): all-gather(q) %.3f x %d, reduce(phi_cur) %.3f x %d, pair all-reduce %.3f x %d, accumulator clear %.3f x %d\n",
+            c->rank, c->nranks, c->comm_calls[0] ? c->comm_ms[0] / c->comm_calls[0] : 0.0, c->comm_calls[0], c->comm_ms[1] / c->comm_calls[1], c->comm_calls[1],
+            c->comm_calls[2] ? c->comm_ms[2] / c->comm_calls[2] : 0.0, c->comm_calls[2], c->comm_calls[3] ? c->comm_ms[3] / c->comm_calls[3] : 0.0, c->comm_calls[3]);
   if (!c)
     return 0;
   cudaSetDevice(c->device);
@@ -1206,6 +1214,38 @@ doma_b200_dump_wait(doma_b200_ctx * c)
   return join_dump(c);
 }
 
+namespace
+{
+// measurement mode (DOMA_B200_COMM_TIMING): device time of one collective, in isolation (synchronises)
+struct CommTimer
+{
+  doma_b200_ctx * c;
+  int slot;
+  cudaEvent_t a = nullptr, b = nullptr;
+  CommTimer(doma_b200_ctx * ctx, int s) : c(ctx), slot(s)
+  {
+    if (!c->comm_timing)
+      return;
+    cudaEventCreate(&a), cudaEventCreate(&b);
+    if (c->nccl_comm && slot < 2 && c->comm_scratch) // align the ranks first, or the time of the first collective after a host gap is rank skew
+      g_nccl.AllReduce(c->comm_scratch, c->comm_scratch, 1, /*ncclDouble*/ 8, /*ncclSum*/ 0, c->nccl_comm, c->stream);
+    cudaStreamSynchronize(c->stream);
+    cudaEventRecord(a, c->stream);
+  }
+  ~CommTimer()
+  {
+    if (!c->comm_timing)
+      return;
+    cudaEventRecord(b, c->stream);
+    cudaEventSynchronize(b);
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, a, b);
+    c->comm_ms[slot] += ms, c->comm_calls[slot] += 1;
+    cudaEventDestroy(a), cudaEventDestroy(b);
+  }
+};
+} // namespace
+
 // ---- angle sharding across ranks: one in-place ncclAllReduce(phi_cur) per sweep ----
 int
 doma_b200_comm_unique_id(char * out, int32_t len)
@@ -1347,13 +1387,22 @@ doma_b200_allreduce_phi_cur(doma_b200_ctx * c)
   int r = 0;
   if (c->cell_sharded)
   {
-    r = g_nccl.ReduceScatter(c->phi_cur, c->phi_red, (size_t)c->slice, /*ncclDouble*/ 8, /*ncclSum*/ 0, c->nccl_comm, c->stream);
+    {
+      CommTimer timer(c, 1);
+      r = g_nccl.ReduceScatter(c->phi_cur, c->phi_red, (size_t)c->slice, /*ncclDouble*/ 8, /*ncclSum*/ 0, c->nccl_comm, c->stream);
+    }
     if (!r)
+    {
+      CommTimer timer(c, 3);
       DOMA_CUDA(c, cudaMemsetAsync(c->phi_cur, 0, sizeof(double) * c->N, c->stream));
+    }
     c->phi_cur_reduced = true;
   }
   else
+  {
+    CommTimer timer(c, 1);
     r = g_nccl.AllReduce(c->phi_cur, c->phi_cur, (size_t)c->N, /*ncclDouble*/ 8, /*ncclSum*/ 0, c->nccl_comm, c->stream);
+  }
   if (r)
   {
     snprintf(c->err, DOMA_MAX_ERR, "%s: %s", c->cell_sharded ? "ncclReduceScatter" : "ncclAllReduce", g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "?");
@@ -1366,11 +1415,13 @@ doma_b200_allreduce_phi_cur(doma_b200_ctx * c)
 } // extern "C"
 
 // ---- collectives the other translation units use ----
+
 int
 doma_comm_gather_q(doma_b200_ctx * c)
 {
   if (!c->cell_sharded || !c->q_slice_only)
     return 0;
+  CommTimer timer(c, 0);
   const int r = g_nccl.AllGather(c->q + c->cell_lo, c->q, (size_t)c->slice, /*ncclDouble*/ 8, c->nccl_comm, c->stream);
   if (r)
   {
@@ -1385,6 +1436,7 @@ doma_comm_gather_q(doma_b200_ctx * c)
 int
 doma_comm_sum_pair(doma_b200_ctx * c)
 {
+  CommTimer timer(c, 2);
   const int r = g_nccl.AllReduce(c->red_out, c->red_out, 2, /*ncclDouble*/ 8, /*ncclSum*/ 0, c->nccl_comm, c->stream);
   if (r)
   {

@@ -103,6 +103,10 @@ struct doma_b200_ctx
 
   // timing / accounting
   cudaEvent_t ev0, ev1;
+  bool comm_timing;           // DOMA_B200_COMM_TIMING=1 at create: every collective is bracketed by events and synchronised (a measurement mode)
+  double comm_ms[4];          // accumulated ms: all-gather(q), reduce-scatter / all-reduce(phi_cur), pair all-reduce, accumulator clear
+  int comm_calls[4];
+  double * comm_scratch;      // 16 bytes for the rank-aligning all-reduce of the timing mode
   bool have_sweep_time;
   int64_t launches;
 
