@@ -449,7 +449,7 @@ doma_b200_destroy(doma_b200_ctx * c)
                    c->sigma_s, c->nu_sigma_f, c->chi_p, c->src, c->inv_v, c->chi_d, c->beta, c->lambda, c->step_t_insert,
                    c->step_t_remove, c->step_src, c->sig_cell, c->phi_tot, c->phi_prev, c->phi_last, c->dnp_cur, c->dnp_last,
                    c->q, c->phi_cur, c->unit_octant, c->u_mu, c->u_eta, c->u_xi, c->u_w, c->tile_order, c->face_x, c->face_y,
-                   c->face_z, c->tile_done, c->work_counter, c->red_partial, c->red_out, c->phi_red, c->gather_tmp, c->si_dev};
+                   c->face_z, c->tile_done, c->work_counter, c->red_partial, c->red_out, c->phi_red, c->gather_tmp, c->si_dev, c->comm_scratch};
   for (void * p : ptrs)
     if (p)
       cudaFree(p);

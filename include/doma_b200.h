@@ -247,6 +247,10 @@ int doma_b200_set_pairing(doma_b200_ctx * ctx, int32_t on);
  * that phi_cur is finite; a missed wavefront dependency then fails the call (error 30) instead of reading last
  * sweep's value.  Costs a synchronisation per sweep. */
 int doma_b200_set_check(doma_b200_ctx * ctx, int32_t on);
+/* Measurement mode, environment variable DOMA_B200_COMM_TIMING=1 at create (multi-rank contexts): every collective
+ * (all-gather of q, reduce-scatter / all-reduce of phi_cur, the 16-byte pair all-reduce, the accumulator clear) is
+ * timed on the device in isolation - ranks aligned first, the stream synchronised - and the means are printed to stderr
+ * by doma_b200_destroy.  Not for timed runs: it serialises the step. */
 /* KBA tile extents in cells; tx is 8 or 4 (the row a warp keeps in registers), tx * ty <= 32; (tx, 0, 0) returns to the
  * library's own choice. Rebuilds the tile table.
  * Without this call the library picks the tile from the mesh size and the number of sweep units (api.cu). */
