@@ -315,3 +315,23 @@ def test_mirror_symmetry_full_size(cuda_lib):
     for ax in range(3):
         assert np.max(np.abs(np.flip(phi, axis=ax) - phi)) <= 1e-11 * np.abs(phi).max()
     assert ctx.last_sweep_ms() > 0
+
+
+def test_set_tile_validation_and_launch_info(cuda_lib):
+    """doma_b200_set_tile: rows of 8 or 4 cells, a slab of at most 32 cells; a rejected tile leaves the old one in place.
+    DOMA_INFO_SWEEP_BLOCKS reports the persistent grid of the last launch (a multiple of the SM count when saturated)."""
+    prob = random_problem((40, 24, 16), G=1, npol=8, nazi=8, seed=3)
+    ctx = abi.Context(prob, cuda_lib)
+    ctx.set_tile(4, 8, 2)
+    assert (ctx.info(abi.INFO_TILE_X), ctx.info(abi.INFO_TILE_Y), ctx.info(abi.INFO_TILE_Z)) == (4, 8, 2)
+    for bad in ((5, 4, 2), (16, 2, 2), (8, 5, 1), (4, 9, 1), (8, 0, 3), (4, 4, 2000)):
+        with pytest.raises(abi.DomaError):
+            ctx.set_tile(*bad)
+        assert (ctx.info(abi.INFO_TILE_X), ctx.info(abi.INFO_TILE_Y), ctx.info(abi.INFO_TILE_Z)) == (4, 8, 2)
+    ctx.set_tile(8, 0, 0)       # back to the library's choice
+    assert ctx.info(abi.INFO_TILE_X) in (4, 8)
+    ctx.reset_state(0.0)
+    ctx.set_array(abi.ARR_Q, 0, np.ones(prob.n_cells))
+    ctx.sweep(0)
+    ctx.synchronize()
+    assert ctx.info(abi.INFO_SWEEP_BLOCKS) > 0
