@@ -38,15 +38,17 @@ def write_case(name, xml):
         f.write("<!-- shipped DOMA case (iteration budget possibly changed) written by tests/golden/make_golden_t3.py -->\n" + xml)
 
 
-def transient(name, xml_path):
-    out_dir = os.path.join(T3, name)
+def transient(name, xml_path, run=None):
+    """Digest of a FINISHED run (directory T3/<run>, log T3/<run>.log) as fixture <name> with the XML it ran."""
+    run = run or name
+    out_dir = os.path.join(T3, run)
     if not os.path.exists(os.path.join(out_dir, "meta.json")):
         print(name, "not finished")
         return
-    d = digest(out_dir, open(os.path.join(T3, name + ".log")).read())
+    d = digest(out_dir, open(os.path.join(T3, run + ".log")).read())
     write_case(name, open(xml_path).read())
     np.savez_compressed(os.path.join(FULL, name + ".npz"), **d)
-    print(f"{name}: ok={d['ok']} sweeps={int(d['si_counts'].sum())} outers={len(d['outer_residuals'])} ref_seconds={d['ref_seconds']:.0f}")
+    print(f"{name}: ok={d['ok']} k={d['k']!r} sweeps={int(d['si_counts'].sum())} outers={len(d['outer_residuals'])} ref_seconds={d['ref_seconds']:.0f}")
 
 
 def snapshots(name, shipped, shape, groups, n_ord, threads, keep):
@@ -90,6 +92,8 @@ def main():
     transient("tr2d_20steps", os.path.join(T3, "tr2d_20steps.xml"))
     transient("tr2d_20steps_remove", os.path.join(T3, "tr2d_20steps_remove.xml"))
     snapshots("asm_eig", "3D_assembly_eig.xml", (152, 152, 38), 3, 128, 4, keep=[2])
+    # the UNMODIFIED shipped eigenvalue case run to its own convergence criterion (k_tol 1e-5): north_star's "k_eff within 1e-9"
+    transient("asm_eig_shipped", os.path.join(REF, "cases", "3D_assembly_eig.xml"), run="asm_eig")
     snapshots("asm_fs", "3D_assembly_fs.xml", (152, 152, 37), 3, 128, 2, keep=[1])
 
 
