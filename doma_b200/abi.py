@@ -217,6 +217,9 @@ class Library:
         "set_cell_sharding": [C.c_void_p, C.c_int32],
         "set_tile": [C.c_void_p, C.c_int32, C.c_int32, C.c_int32],
         "source_iteration": [C.c_void_p, C.c_int32, C.c_double, C.c_int32, C.POINTER(C.c_int32), _pd, _pd],
+        # context-free, allocation-free residual on caller-provided device pointers (static device scratch; see the header)
+        "scatter_residual_noalloc": [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
+                                     C.c_void_p, C.c_void_p, _pd, C.c_char_p, C.c_int32],
     }
 
     def __init__(self, path: str = LIB_PATH, prefix: str = "doma_b200_"):

@@ -181,6 +181,26 @@ int doma_b200_set_cell_sharding(doma_b200_ctx * ctx, int32_t on);
 /* reductions (each synchronises and returns scalars) ------------------------------------------- */
 /* computeScatteringResidual(g) (3D:547-563) */
 int doma_b200_scatter_residual(doma_b200_ctx * ctx, int32_t g, double * out);
+/* The same residual for callers that cannot let the library allocate (CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * It needs no context and calls no cudaMalloc / cudaFree / allocating routine: the reduction's scratch (one pair of
+ * partial sums per block of DOMA_NOALLOC_CELLS_PER_BLOCK cells + the final pair) is a file-scope __device__ array of
+ * DOMA_NOALLOC_SCRATCH_BYTES that every GPU loading the library holds until exit.  Limit: nx*ny*nz <=
+ * DOMA_NOALLOC_MAX_CELLS, more is rejected (error 40 + message).  All calls on a device share the array: a call reads
+ * only slots it has written itself, so nothing needs clearing between calls, but calls that OVERLAP on the GPU (other
+ * streams, concurrent graph branches) race on it and must be serialised by the caller.
+ *   inputs  (device): phi_tot_g[N], phi_cur[N] (reference cell order), dx[nx], dy[ny], dz[nz] (dz ignored for dims = 2)
+ *   outputs: sums_out_dev[2] (device) = { sum V cur^2, sum V (tot+cur)^2 }, written on cuda_stream (a cudaStream_t, may
+ *            be NULL = the default stream); residual_out_host (may be NULL): when given, the call synchronises the
+ *            stream and stores total > 1e-8 ? sqrt(diff)/sqrt(total) : 0 (3D:562) there.
+ *   err_out (may be NULL): receives the message of a non-zero return.  1 = bad argument, 40 = too many cells, 100 + e = CUDA. */
+#define DOMA_NOALLOC_CELLS_PER_BLOCK 4096
+#define DOMA_NOALLOC_MAX_CELLS 33554432LL  /* 8 192 blocks x 4 096 cells: twice the 256^3 bench mesh */
+#define DOMA_NOALLOC_SCRATCH_BYTES 131328  /* 2 x 8 192 partial sums + 32 doubles of tail, per GPU */
+int doma_b200_scatter_residual_noalloc(const double * phi_tot_g_dev, const double * phi_cur_dev, const double * dx_dev,
+                                       const double * dy_dev, const double * dz_dev, int32_t dims, int32_t nx, int32_t ny, int32_t nz,
+                                       void * cuda_stream, double * sums_out_dev, double * residual_out_host, char * err_out,
+                                       int32_t err_len);
 /* computeMGFluxResidual() (3D:318-337) */
 int doma_b200_mg_residual(doma_b200_ctx * ctx, double * out);
 /* updateEigenvalue() (3D:432-456): k_prev_out = *k_inout; *k_inout = num/den */
