@@ -55,8 +55,8 @@ for W in [int(w) for w in a.worlds.split(",")]:
             if tile == "auto":
                 ctx.set_tile(8, 0, 0)
             else:
-                ty, tz = [int(v) for v in tile.split("x")]
-                ctx.set_tile(8, ty, tz)
+                t = [int(v) for v in tile.split("x")]          # TYxTZ (8-cell rows) or TXxTYxTZ
+                ctx.set_tile(*(t if len(t) == 3 else [8] + t))
             ts = []
             for i in range(2 + a.reps):
                 if i == 1 + a.reps:         # last repetition: from a clean phi_cur, for the comparison
