@@ -72,7 +72,9 @@ def test_driver_fast_dump_writes_the_reference_files(name, tmp_path):
 # ---- the drop-in at FULL size: the reference's own loops + libdoma_b200.so against the reference's digests ----
 FULL_CASES = ["k1", "asm_fs_3outer", "asm_eig_3pi", "tr2d_1step", "syn256_b",
               # T3: the shipped source-iteration budgets over several outer iterations / 20 time steps (tests/golden/make_golden_t3.py)
-              "asm_eig_t3_3outer", "asm_fs_t3_2outer", "tr2d_20steps_remove"]
+              "asm_eig_t3_3outer", "asm_fs_t3_2outer", "tr2d_20steps_remove",
+              # the UNMODIFIED shipped eigenvalue case, run by the reference to its own convergence criterion (16 power iterations, 6 256 sweeps)
+              "asm_eig_shipped"]
 
 
 @pytest.mark.parametrize("name", FULL_CASES)
